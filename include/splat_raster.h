@@ -1,0 +1,116 @@
+/* splat_raster.h — C ABI of the B200-native differentiable Gaussian-splatting rasterizer with pose gradients.
+ *
+ * Drop-in boundary for the path Splat-SLAM reaches through `diff_gaussian_rasterization._C`
+ * (DGR = thirdparty/diff-gaussian-rasterization-w-pose in the reference tree):
+ *   _C.rasterize_gaussians            DGR/rasterize_points.cu:35-122   -> CudaRasterizer::Rasterizer::forward  (DGR/cuda_rasterizer/rasterizer.h:33-59,  rasterizer_impl.cu:198-344)
+ *   _C.rasterize_gaussians_backward   DGR/rasterize_points.cu:124-211  -> CudaRasterizer::Rasterizer::backward (DGR/cuda_rasterizer/rasterizer.h:61-91,  rasterizer_impl.cu:348-455)
+ *   _C.mark_visible                   DGR/rasterize_points.cu:213-232  -> CudaRasterizer::Rasterizer::markVisible (DGR/cuda_rasterizer/rasterizer.h:24-31, rasterizer_impl.cu:141-153)
+ *
+ * Conventions
+ *   - plain C: device pointers, ints/floats, a cudaStream_t passed as void*; no torch types, no exceptions.
+ *   - every function returns 0 on success, a positive cudaError_t value if a launch/runtime call failed,
+ *     or a negative SPLAT_ERR_* code for bad arguments. Kernel faults surface asynchronously, as in the reference
+ *     (its CHECK_CUDA only synchronises when debug=true, DGR/cuda_rasterizer/auxiliary.h:166-173).
+ *   - the library never allocates or frees device memory: the caller owns inputs, outputs and the three opaque
+ *     state buffers (geometry / binning / image), sized by the *_bytes queries below. This replaces the
+ *     reference's std::function resize callbacks (DGR/rasterize_points.cu:27-33, rasterizer_impl.cu:228-243,286-288).
+ *   - all float tensors are contiguous float32, matrices are the 16 floats the reference receives
+ *     (viewmatrix = W2C^T i.e. column-major W2C, projmatrix = viewmatrix @ projmatrix_raw).
+ *   - optional inputs are passed as NULL exactly where the reference passes an empty tensor
+ *     (shs XOR colors_precomp; (scales, rotations) XOR cov3D_precomp).
+ *   - work is enqueued on `stream`; nothing synchronises the device.
+ */
+#ifndef SPLAT_RASTER_H_
+#define SPLAT_RASTER_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SPLAT_OK 0
+#define SPLAT_ERR_ARG (-1)   /* NULL / inconsistent argument */
+#define SPLAT_ERR_SIZE (-2)  /* negative or overflowing size */
+
+/* ABI version of this header (bumped on any signature change). */
+int splat_raster_abi_version(void);
+
+/* Sizes of the caller-allocated opaque state buffers.
+ * Replace `required<GeometryState/ImageState/BinningState>` (DGR/cuda_rasterizer/rasterizer_impl.h:65-72). */
+size_t splat_raster_geom_bytes(int P);
+size_t splat_raster_image_bytes(int W, int H);
+size_t splat_raster_binning_bytes(int R);
+
+/* Forward, stage 1 of 2: per-Gaussian preprocess + instance-offset scan.
+ * Replaces FORWARD::preprocess + cub::DeviceScan::InclusiveSum (DGR/cuda_rasterizer/rasterizer_impl.cu:250-280,
+ * forward.cu:158-258). Writes radii[P] (int32), zeroes n_touched[P] (int32), fills `geom`, and leaves the number of
+ * tile instances R = num_rendered both in `geom` and, if `num_rendered_host` is not NULL, in that (pinned) host
+ * int via an async copy on `stream` — the caller synchronises the stream, reads R and sizes the binning buffer,
+ * which is the same single device->host hand-off the reference has (rasterizer_impl.cu:284). */
+int splat_raster_forward_preprocess(
+    int P, int D, int M, int W, int H,
+    const float* means3D, const float* scales, float scale_modifier, const float* rotations,
+    const float* opacities, const float* shs, const float* cov3D_precomp, const float* colors_precomp,
+    const float* viewmatrix, const float* projmatrix, const float* campos,
+    float tan_fovx, float tan_fovy, int prefiltered,
+    int* radii, int* n_touched, void* geom, int* num_rendered_host, void* stream);
+
+/* Forward, stage 2 of 2: key generation, 64-bit (tile|depth) radix sort, tile ranges, render.
+ * Replaces duplicateWithKeys, cub::DeviceRadixSort::SortPairs, identifyTileRanges and FORWARD::render
+ * (DGR/cuda_rasterizer/rasterizer_impl.cu:286-341, forward.cu:263-392).
+ * out_color[3*H*W], out_depth[H*W], out_opacity[H*W] are fully written; n_touched[P] is accumulated into. */
+int splat_raster_forward_render(
+    int P, int R, int W, int H, const float* background, const float* colors_precomp, const int* radii,
+    void* geom, void* binning, void* image,
+    float* out_color, float* out_depth, float* out_opacity, int* n_touched, void* stream);
+
+/* Backward. Replaces CudaRasterizer::Rasterizer::backward (DGR/cuda_rasterizer/rasterizer_impl.cu:348-455):
+ * BACKWARD::render (backward.cu:563-787) then computeCov2DCUDA + preprocessCUDA (backward.cu:150-346,418-539).
+ *   grad_scratch : P * 12 floats of scratch, cleared by this call (packed per-Gaussian render gradients)
+ *   dL_dtau_partial : ceil(P/256) * 6 floats; the camera-pose gradient is the column sum
+ *                     (rho = [0:3], theta = [3:6]) — the reference returns P x 6 and sums in Python
+ *                     (DGR/diff_gaussian_rasterization/__init__.py:152-154)
+ * All other outputs are fully written, zeros for culled Gaussians: dL_dmeans2D[P*3], dL_dcolors[P*3],
+ * dL_dopacity[P], dL_dmeans3D[P*3], dL_dcov3D[P*6], dL_dsh[P*M*3] (if shs), dL_dscales[P*3] and
+ * dL_drotations[P*4] (if scales). */
+int splat_raster_backward(
+    int P, int D, int M, int R, int W, int H,
+    const float* background, const float* means3D, const float* shs, const float* colors_precomp,
+    const float* scales, float scale_modifier, const float* rotations, const float* cov3D_precomp,
+    const float* viewmatrix, const float* projmatrix, const float* projmatrix_raw, const float* campos,
+    float tan_fovx, float tan_fovy, const int* radii,
+    void* geom, void* binning, void* image,
+    const float* dL_dout_color, const float* dL_dout_depth,
+    float* grad_scratch,
+    float* dL_dmeans2D, float* dL_dcolors, float* dL_dopacity, float* dL_dmeans3D, float* dL_dcov3D,
+    float* dL_dsh, float* dL_dscales, float* dL_drotations, float* dL_dtau_partial, void* stream);
+
+/* present[i] = Gaussian i passes the near-plane test. Replaces Rasterizer::markVisible / checkFrustum
+ * (DGR/cuda_rasterizer/rasterizer_impl.cu:54-66,141-153). `present` is P bytes (bool). */
+int splat_raster_mark_visible(int P, const float* means3D, const float* viewmatrix, const float* projmatrix,
+                              unsigned char* present, void* stream);
+
+/* Test/diagnostic view into the opaque buffers (device pointers into the caller's buffers; layout is private).
+ * Mirrors what the parity harness carves out of the reference's buffers (rasterizer_impl.cu:155-194). */
+typedef struct splat_raster_views {
+    const float* depths;              /* [P] */
+    const float* means2D;             /* [P*2] */
+    const float* conic_opacity;       /* [P*4] */
+    const float* rgb;                 /* [P*3] */
+    const float* cov3D;               /* [P*6] */
+    const unsigned int* tiles_touched;/* [P] */
+    const unsigned long long* keys;   /* [R] sorted keys */
+    const unsigned int* point_list;   /* [R] sorted Gaussian ids */
+    const unsigned int* ranges;       /* [tiles*2] */
+    const float* final_T;             /* [H*W] */
+    const unsigned int* n_contrib;    /* [H*W] */
+} splat_raster_views;
+int splat_raster_debug_views(int P, int R, int W, int H, void* geom, void* binning, void* image,
+                             splat_raster_views* out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SPLAT_RASTER_H_ */

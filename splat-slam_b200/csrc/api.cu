@@ -1,0 +1,186 @@
+// extern "C" entry points declared in include/splat_raster.h: argument checks, state carving, launch sequences.
+#include "../../include/splat_raster.h"
+#include "common.cuh"
+#include "kernels.h"
+
+using namespace splat;
+
+namespace {
+inline int grid_dim(int v) { return (v + SPLAT_TILE - 1) / SPLAT_TILE; }
+}  // namespace
+
+extern "C" {
+
+int splat_raster_abi_version(void) { return 1; }
+
+size_t splat_raster_geom_bytes(int P) {
+    if (P < 0) return 0;
+    size_t b = 0;
+    GeomState::carve(nullptr, (size_t)P, &b);
+    return b;
+}
+
+size_t splat_raster_image_bytes(int W, int H) {
+    if (W <= 0 || H <= 0) return 0;
+    size_t b = 0;
+    ImageState::carve(nullptr, (size_t)W * H, (size_t)grid_dim(W) * grid_dim(H), &b);
+    return b;
+}
+
+size_t splat_raster_binning_bytes(int R) {
+    if (R < 0) return 0;
+    size_t b = 0;
+    BinningState::carve(nullptr, (size_t)R, &b);
+    return b;
+}
+
+int splat_raster_forward_preprocess(int P, int D, int M, int W, int H, const float* means3D, const float* scales,
+                                    float scale_modifier, const float* rotations, const float* opacities,
+                                    const float* shs, const float* cov3D_precomp, const float* colors_precomp,
+                                    const float* viewmatrix, const float* projmatrix, const float* campos,
+                                    float tan_fovx, float tan_fovy, int prefiltered, int* radii, int* n_touched,
+                                    void* geom, int* num_rendered_host, void* stream) {
+    if (P < 0 || W <= 0 || H <= 0 || D < 0 || D > 3) return SPLAT_ERR_SIZE;
+    if (!geom || !viewmatrix || !projmatrix) return SPLAT_ERR_ARG;
+    cudaStream_t s = (cudaStream_t)stream;
+    GeomState g = GeomState::carve(geom, (size_t)P, nullptr);
+    if (P == 0) {
+        cudaMemsetAsync(g.num_rendered, 0, sizeof(uint32_t), s);
+        if (num_rendered_host) *num_rendered_host = 0;
+        return SPLAT_OK;
+    }
+    if (!means3D || !opacities || !radii || !n_touched) return SPLAT_ERR_ARG;
+    if ((shs == nullptr) == (colors_precomp == nullptr)) return SPLAT_ERR_ARG;            // exactly one colour source
+    if (((scales == nullptr) || (rotations == nullptr)) == (cov3D_precomp == nullptr)) return SPLAT_ERR_ARG;
+    if (shs && (M < (D + 1) * (D + 1) || !campos)) return SPLAT_ERR_ARG;
+    FwdParams p;
+    p.P = P; p.D = D; p.M = M; p.W = W; p.H = H;
+    p.grid_x = grid_dim(W); p.grid_y = grid_dim(H);
+    p.prefiltered = prefiltered;
+    p.scale_modifier = scale_modifier; p.tanfovx = tan_fovx; p.tanfovy = tan_fovy;
+    // focal lengths exactly as the reference derives them on the host (rasterizer_impl.cu:225-226)
+    p.focal_y = H / (2.0f * tan_fovy);
+    p.focal_x = W / (2.0f * tan_fovx);
+    p.means3D = means3D; p.scales = scales; p.rotations = rotations; p.opacities = opacities; p.shs = shs;
+    p.cov3D_precomp = cov3D_precomp; p.colors_precomp = colors_precomp;
+    p.viewmatrix = viewmatrix; p.projmatrix = projmatrix; p.campos = campos;
+    p.radii = radii; p.n_touched = n_touched;
+    launch_preprocess_forward(p, g, s);
+    SPLAT_CUDA_CHECK_LAUNCH();
+    launch_scan_block_sums(P, g, s);
+    SPLAT_CUDA_CHECK_LAUNCH();
+    if (num_rendered_host) {
+        cudaError_t e = cudaMemcpyAsync(num_rendered_host, g.num_rendered, sizeof(int), cudaMemcpyDeviceToHost, s);
+        if (e != cudaSuccess) return (int)e;
+    }
+    return SPLAT_OK;
+}
+
+int splat_raster_forward_render(int P, int R, int W, int H, const float* background, const float* colors_precomp,
+                                const int* radii, void* geom, void* binning, void* image, float* out_color,
+                                float* out_depth, float* out_opacity, int* n_touched, void* stream) {
+    if (P < 0 || R < 0 || W <= 0 || H <= 0) return SPLAT_ERR_SIZE;
+    if (!geom || !binning || !image || !background || !out_color || !out_depth || !out_opacity) return SPLAT_ERR_ARG;
+    if (P > 0 && (!radii || !n_touched)) return SPLAT_ERR_ARG;
+    cudaStream_t s = (cudaStream_t)stream;
+    const int gx = grid_dim(W), gy = grid_dim(H);
+    GeomState g = GeomState::carve(geom, (size_t)P, nullptr);
+    BinningState b = BinningState::carve(binning, (size_t)R, nullptr);
+    ImageState im = ImageState::carve(image, (size_t)W * H, (size_t)gx * gy, nullptr);
+    const int passes = sort_passes(gx, gy);
+    if (R > 0) {
+        // unsorted keys go where an odd/even number of ping-pong passes ends in b.keys / b.point_list
+        uint64_t* k0 = (passes & 1) ? b.keys_alt : b.keys;
+        uint32_t* v0 = (passes & 1) ? b.vals_alt : b.point_list;
+        launch_duplicate_with_keys(P, gx, gy, radii, g, k0, v0, s);
+        SPLAT_CUDA_CHECK_LAUNCH();
+        launch_radix_sort(R, passes, b, s);
+        SPLAT_CUDA_CHECK_LAUNCH();
+    }
+    launch_ranges_and_records(R, gx * gy, colors_precomp, g, b, im.ranges, s);
+    SPLAT_CUDA_CHECK_LAUNCH();
+    launch_render_forward(W, H, gx, gy, im.ranges, b.records, background, im.final_T, im.n_contrib, out_color,
+                          out_depth, out_opacity, n_touched, s);
+    SPLAT_CUDA_CHECK_LAUNCH();
+    return SPLAT_OK;
+}
+
+int splat_raster_backward(int P, int D, int M, int R, int W, int H, const float* background, const float* means3D,
+                          const float* shs, const float* colors_precomp, const float* scales, float scale_modifier,
+                          const float* rotations, const float* cov3D_precomp, const float* viewmatrix,
+                          const float* projmatrix, const float* projmatrix_raw, const float* campos, float tan_fovx,
+                          float tan_fovy, const int* radii, void* geom, void* binning, void* image,
+                          const float* dL_dout_color, const float* dL_dout_depth, float* grad_scratch,
+                          float* dL_dmeans2D, float* dL_dcolors, float* dL_dopacity, float* dL_dmeans3D,
+                          float* dL_dcov3D, float* dL_dsh, float* dL_dscales, float* dL_drotations,
+                          float* dL_dtau_partial, void* stream) {
+    if (P < 0 || R < 0 || W <= 0 || H <= 0 || D < 0 || D > 3) return SPLAT_ERR_SIZE;
+    if (P == 0) return SPLAT_OK;
+    if (!geom || !binning || !image || !background || !means3D || !radii || !viewmatrix || !projmatrix ||
+        !projmatrix_raw || !dL_dout_color || !dL_dout_depth || !grad_scratch || !dL_dmeans2D || !dL_dcolors ||
+        !dL_dopacity || !dL_dmeans3D || !dL_dcov3D || !dL_dtau_partial)
+        return SPLAT_ERR_ARG;
+    if (shs && (!dL_dsh || !campos)) return SPLAT_ERR_ARG;
+    if (scales && (!rotations || !dL_dscales || !dL_drotations)) return SPLAT_ERR_ARG;
+    cudaStream_t s = (cudaStream_t)stream;
+    const int gx = grid_dim(W), gy = grid_dim(H);
+    GeomState g = GeomState::carve(geom, (size_t)P, nullptr);
+    BinningState b = BinningState::carve(binning, (size_t)R, nullptr);
+    ImageState im = ImageState::carve(image, (size_t)W * H, (size_t)gx * gy, nullptr);
+    cudaError_t e = cudaMemsetAsync(grad_scratch, 0, sizeof(float) * SPLAT_GRAD_FLOATS * (size_t)P, s);
+    if (e != cudaSuccess) return (int)e;
+    if (R > 0) {
+        launch_render_backward(W, H, gx, gy, im.ranges, b.records, background, im.final_T, im.n_contrib, dL_dout_color,
+                               dL_dout_depth, grad_scratch, s);
+        SPLAT_CUDA_CHECK_LAUNCH();
+    }
+    BwdParams p;
+    p.P = P; p.D = D; p.M = M; p.R = R; p.W = W; p.H = H; p.grid_x = gx; p.grid_y = gy;
+    p.scale_modifier = scale_modifier; p.tanfovx = tan_fovx; p.tanfovy = tan_fovy;
+    p.focal_y = H / (2.0f * tan_fovy);
+    p.focal_x = W / (2.0f * tan_fovx);
+    p.bg = background; p.means3D = means3D; p.shs = shs; p.colors_precomp = colors_precomp; p.scales = scales;
+    p.rotations = rotations; p.cov3D_precomp = cov3D_precomp; p.viewmatrix = viewmatrix; p.projmatrix = projmatrix;
+    p.projmatrix_raw = projmatrix_raw; p.campos = campos; p.radii = radii;
+    p.dL_dpix = dL_dout_color; p.dL_dpix_depth = dL_dout_depth; p.grad_accum = grad_scratch;
+    p.dL_dmean2D = dL_dmeans2D; p.dL_dcolors = dL_dcolors; p.dL_dopacity = dL_dopacity; p.dL_dmean3D = dL_dmeans3D;
+    p.dL_dcov3D = dL_dcov3D; p.dL_dsh = dL_dsh; p.dL_dscale = dL_dscales; p.dL_drot = dL_drotations;
+    p.dL_dtau = dL_dtau_partial;
+    launch_preprocess_backward(p, g, s);
+    SPLAT_CUDA_CHECK_LAUNCH();
+    return SPLAT_OK;
+}
+
+int splat_raster_mark_visible(int P, const float* means3D, const float* viewmatrix, const float* projmatrix,
+                              unsigned char* present, void* stream) {
+    (void)projmatrix;   // the reference's test only uses the view-space depth (auxiliary.h:154)
+    if (P < 0) return SPLAT_ERR_SIZE;
+    if (P == 0) return SPLAT_OK;
+    if (!means3D || !viewmatrix || !present) return SPLAT_ERR_ARG;
+    launch_mark_visible(P, means3D, viewmatrix, reinterpret_cast<bool*>(present), (cudaStream_t)stream);
+    SPLAT_CUDA_CHECK_LAUNCH();
+    return SPLAT_OK;
+}
+
+int splat_raster_debug_views(int P, int R, int W, int H, void* geom, void* binning, void* image,
+                             splat_raster_views* out) {
+    if (!out || P < 0 || R < 0 || W <= 0 || H <= 0) return SPLAT_ERR_ARG;
+    const int gx = grid_dim(W), gy = grid_dim(H);
+    GeomState g = GeomState::carve(geom, (size_t)P, nullptr);
+    BinningState b = BinningState::carve(binning, (size_t)R, nullptr);
+    ImageState im = ImageState::carve(image, (size_t)W * H, (size_t)gx * gy, nullptr);
+    out->depths = g.depths;
+    out->means2D = reinterpret_cast<const float*>(g.means2D);
+    out->conic_opacity = reinterpret_cast<const float*>(g.conic_opacity);
+    out->rgb = g.rgb;
+    out->cov3D = g.cov3D;
+    out->tiles_touched = g.tiles_touched;
+    out->keys = reinterpret_cast<const unsigned long long*>(b.keys);
+    out->point_list = b.point_list;
+    out->ranges = reinterpret_cast<const unsigned int*>(im.ranges);
+    out->final_T = im.final_T;
+    out->n_contrib = im.n_contrib;
+    return SPLAT_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,50 @@
+// Internal launch interface between api.cu and the kernel translation units.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "state.h"
+
+namespace splat {
+
+struct FwdParams {
+    int P, D, M, W, H, grid_x, grid_y, prefiltered;
+    float scale_modifier, tanfovx, tanfovy, focal_x, focal_y;
+    const float *means3D, *scales, *rotations, *opacities, *shs, *cov3D_precomp, *colors_precomp;
+    const float *viewmatrix, *projmatrix, *campos;
+    int* radii;
+    int* n_touched;
+};
+
+struct BwdParams {
+    int P, D, M, R, W, H, grid_x, grid_y;
+    float scale_modifier, tanfovx, tanfovy, focal_x, focal_y;
+    const float *bg, *means3D, *shs, *colors_precomp, *scales, *rotations, *cov3D_precomp;
+    const float *viewmatrix, *projmatrix, *projmatrix_raw, *campos;
+    const int* radii;
+    const float *dL_dpix, *dL_dpix_depth;
+    float* grad_accum;  // [P * SPLAT_GRAD_FLOATS], zeroed by the caller-visible entry point
+    float *dL_dmean2D, *dL_dcolors, *dL_dopacity, *dL_dmean3D, *dL_dcov3D, *dL_dsh, *dL_dscale, *dL_drot, *dL_dtau;
+};
+
+// preprocess.cu
+void launch_preprocess_forward(const FwdParams& p, const GeomState& g, cudaStream_t s);
+void launch_mark_visible(int P, const float* means3D, const float* viewmatrix, bool* present, cudaStream_t s);
+// preprocess_bwd.cu
+void launch_preprocess_backward(const BwdParams& p, const GeomState& g, cudaStream_t s);
+// binning.cu
+void launch_scan_block_sums(int P, const GeomState& g, cudaStream_t s);
+void launch_duplicate_with_keys(int P, int grid_x, int grid_y, const int* radii, const GeomState& g,
+                                uint64_t* keys_out, uint32_t* vals_out, cudaStream_t s);
+int sort_passes(int grid_x, int grid_y);
+void launch_radix_sort(int R, int passes, const BinningState& b, cudaStream_t s);
+void launch_ranges_and_records(int R, int tiles, const float* colors_precomp, const GeomState& g,
+                               const BinningState& b, uint2* ranges, cudaStream_t s);
+// render.cu
+void launch_render_forward(int W, int H, int grid_x, int grid_y, const uint2* ranges, const float* records,
+                           const float* bg, float* final_T, uint32_t* n_contrib, float* out_color, float* out_depth,
+                           float* out_opacity, int* n_touched, cudaStream_t s);
+void launch_render_backward(int W, int H, int grid_x, int grid_y, const uint2* ranges, const float* records,
+                            const float* bg, const float* final_T, const uint32_t* n_contrib, const float* dL_dpix,
+                            const float* dL_dpix_depth, float* grad_accum, cudaStream_t s);
+
+}  // namespace splat

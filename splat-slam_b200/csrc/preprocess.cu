@@ -1,0 +1,223 @@
+// Per-Gaussian forward stage: near cull, 3D covariance, EWA 2D covariance, conic, radius, tile rectangle,
+// SH -> RGB, and the per-block tile count that feeds the offset scan.
+// Replaces DGR/cuda_rasterizer/forward.cu:158-258 (preprocessCUDA) and rasterizer_impl.cu:54-66 (checkFrustum).
+#include <cstdio>
+#include "common.cuh"
+#include "kernels.h"
+
+namespace splat {
+
+// SH basis constants (DGR/cuda_rasterizer/auxiliary.h:20-39)
+__device__ const float kSH_C0 = 0.28209479177387814f;
+__device__ const float kSH_C1 = 0.4886025119029199f;
+__device__ const float kSH_C2[5] = {1.0925484305920792f, -1.0925484305920792f, 0.31539156525252005f,
+                                    -1.0925484305920792f, 0.5462742152960396f};
+__device__ const float kSH_C3[7] = {-0.5900435899266435f, 2.890611442640554f, -0.4570457994644658f,
+                                    0.3731763325901154f, -0.4570457994644658f, 1.445305721320277f,
+                                    -0.5900435899266435f};
+
+// SH -> RGB with +0.5 and clamp at 0 (DGR forward.cu:22-73). Colours only need 1e-5, so plain float code.
+__device__ __forceinline__ float3 sh_to_rgb(int deg, int M, const float* __restrict__ sh, float3 pos, float3 campos,
+                                            uint8_t& clamp_bits) {
+    float3 dir = make_float3(pos.x - campos.x, pos.y - campos.y, pos.z - campos.z);
+    const float len = sqrtf(dir.x * dir.x + dir.y * dir.y + dir.z * dir.z);
+    dir.x /= len; dir.y /= len; dir.z /= len;
+    const float3* c = reinterpret_cast<const float3*>(sh);
+    (void)M;
+    float3 r = make_float3(kSH_C0 * c[0].x, kSH_C0 * c[0].y, kSH_C0 * c[0].z);
+    if (deg > 0) {
+        const float x = dir.x, y = dir.y, z = dir.z;
+#define SH_ACC(w, k) { const float w__ = (w); r.x += w__ * c[k].x; r.y += w__ * c[k].y; r.z += w__ * c[k].z; }
+        SH_ACC(-kSH_C1 * y, 1) SH_ACC(kSH_C1 * z, 2) SH_ACC(-kSH_C1 * x, 3)
+        if (deg > 1) {
+            const float xx = x * x, yy = y * y, zz = z * z, xy = x * y, yz = y * z, xz = x * z;
+            SH_ACC(kSH_C2[0] * xy, 4) SH_ACC(kSH_C2[1] * yz, 5) SH_ACC(kSH_C2[2] * (2.0f * zz - xx - yy), 6)
+            SH_ACC(kSH_C2[3] * xz, 7) SH_ACC(kSH_C2[4] * (xx - yy), 8)
+            if (deg > 2) {
+                SH_ACC(kSH_C3[0] * y * (3.0f * xx - yy), 9) SH_ACC(kSH_C3[1] * xy * z, 10)
+                SH_ACC(kSH_C3[2] * y * (4.0f * zz - xx - yy), 11)
+                SH_ACC(kSH_C3[3] * z * (2.0f * zz - 3.0f * xx - 3.0f * yy), 12)
+                SH_ACC(kSH_C3[4] * x * (4.0f * zz - xx - yy), 13) SH_ACC(kSH_C3[5] * z * (xx - yy), 14)
+                SH_ACC(kSH_C3[6] * x * (xx - 3.0f * yy), 15)
+            }
+        }
+#undef SH_ACC
+    }
+    r.x += 0.5f; r.y += 0.5f; r.z += 0.5f;
+    clamp_bits = (r.x < 0.0f ? 1 : 0) | (r.y < 0.0f ? 2 : 0) | (r.z < 0.0f ? 4 : 0);
+    return make_float3(fmaxf(r.x, 0.0f), fmaxf(r.y, 0.0f), fmaxf(r.z, 0.0f));
+}
+
+// Sigma = (S R)^T (S R) from scale and the UN-normalised quaternion (r,x,y,z) (DGR forward.cu:120-154).
+// Rounding sequence reproduces the reference SASS: six cross terms are fma(u,v,+-(w*t)) with the rounded
+// product being r*z, x*z and r*x respectively; squares are y*y, z*z rounded and x*x fused.
+__device__ __forceinline__ void cov3d_ref(float sx, float sy, float sz, float mod, float4 q, float* cov) {
+    const float r = q.x, x = q.y, y = q.z, z = q.w;
+    const float yy = fmul(y, y), zz = fmul(z, z);
+    const float rz = fmul(r, z), xz = fmul(x, z), rx = fmul(r, x);
+    const float xy_m_rz = ffma(x, y, -rz), xy_p_rz = ffma(x, y, rz);
+    const float xz_p_ry = ffma(r, y, xz), xz_m_ry = ffma(-r, y, xz);
+    const float yz_m_rx = ffma(y, z, -rx), yz_p_rx = ffma(y, z, rx);
+    const float xx_zz = ffma(x, x, zz), xx_yy = ffma(x, x, yy), yy_zz = fadd(yy, zz);
+    // rotation rows in the order the reference passes them to glm::mat3 (as columns)
+    const float R00 = fsub(1.0f, fadd(yy_zz, yy_zz)), R01 = fadd(xy_m_rz, xy_m_rz), R02 = fadd(xz_p_ry, xz_p_ry);
+    const float R10 = fadd(xy_p_rz, xy_p_rz), R11 = fsub(1.0f, fadd(xx_zz, xx_zz)), R12 = fadd(yz_m_rx, yz_m_rx);
+    const float R20 = fadd(xz_m_ry, xz_m_ry), R21 = fadd(yz_p_rx, yz_p_rx), R22 = fsub(1.0f, fadd(xx_yy, xx_yy));
+    const float s0 = fmul(mod, sx), s1 = fmul(mod, sy), s2 = fmul(mod, sz);
+    // M (glm) column c = s (.) R-row c
+    const float m00 = fmul(s0, R00), m01 = fmul(s1, R01), m02 = fmul(s2, R02);
+    const float m10 = fmul(s0, R10), m11 = fmul(s1, R11), m12 = fmul(s2, R12);
+    const float m20 = fmul(s0, R20), m21 = fmul(s1, R21), m22 = fmul(s2, R22);
+    cov[0] = dot3_ref(m00, m00, m01, m01, m02, m02);
+    cov[1] = dot3_ref(m10, m00, m11, m01, m12, m02);
+    cov[2] = dot3_ref(m20, m00, m21, m01, m22, m02);
+    cov[3] = dot3_ref(m10, m10, m11, m11, m12, m12);
+    cov[4] = dot3_ref(m20, m10, m21, m11, m22, m12);
+    cov[5] = dot3_ref(m20, m20, m21, m21, m22, m22);
+}
+
+// EWA projection of the 3D covariance with the 1.3*tanfov guard band and the 0.3 low-pass
+// (DGR forward.cu:76-115). t = view-space mean (already computed, identical ops). Returns (a, b, c).
+__device__ __forceinline__ float3 cov2d_ref(float tx, float ty, float tz, float fx, float fy, float tanfovx,
+                                            float tanfovy, const float* cov, const float* __restrict__ V) {
+    const float limx = fmul(tanfovx, 1.3f), limy = fmul(tanfovy, 1.3f);
+    const float txtz = __fdiv_rn(tx, tz), tytz = __fdiv_rn(ty, tz);
+    const float cxl = fminf(limx, fmaxf(-limx, txtz));
+    const float cyl = fminf(limy, fmaxf(-limy, tytz));
+    const float tz2 = fmul(tz, tz);
+    const float J00 = __fdiv_rn(fx, tz);
+    const float J02 = __fdiv_rn(fmul(fx, fmul(cxl, -tz)), tz2);
+    const float J11 = __fdiv_rn(fy, tz);
+    const float J12 = __fdiv_rn(fmul(fy, fmul(cyl, -tz)), tz2);
+    float T0[3], T1[3];
+#pragma unroll
+    for (int r = 0; r < 3; ++r) {
+        T0[r] = ffma(V[4 * r + 2], J02, fmul(V[4 * r], J00));
+        T1[r] = ffma(V[4 * r + 2], J12, fmul(J11, V[4 * r + 1]));
+    }
+    const float v0[3] = {cov[0], cov[1], cov[2]}, v1[3] = {cov[1], cov[3], cov[4]}, v2[3] = {cov[2], cov[4], cov[5]};
+    const float X00 = dot3_ref(T0[0], v0[0], T0[1], v0[1], T0[2], v0[2]);
+    const float X01 = dot3_ref(T1[0], v0[0], T1[1], v0[1], T1[2], v0[2]);
+    const float X10 = dot3_ref(T0[0], v1[0], T0[1], v1[1], T0[2], v1[2]);
+    const float X11 = dot3_ref(T1[0], v1[0], T1[1], v1[1], T1[2], v1[2]);
+    const float X20 = dot3_ref(T0[0], v2[0], T0[1], v2[1], T0[2], v2[2]);
+    const float X21 = dot3_ref(T1[0], v2[0], T1[1], v2[1], T1[2], v2[2]);
+    const float c00 = dot3_ref(T0[0], X00, T0[1], X10, T0[2], X20);
+    const float c01 = dot3_ref(T0[0], X01, T0[1], X11, T0[2], X21);
+    const float c11 = dot3_ref(T1[0], X01, T1[1], X11, T1[2], X21);
+    return make_float3(fadd(c00, 0.3f), c01, fadd(c11, 0.3f));
+}
+
+__global__ void __launch_bounds__(kPreBlock)
+preprocess_forward_kernel(int P, int D, int M,
+                          const float* __restrict__ means3D, const float* __restrict__ scales, float scale_modifier,
+                          const float* __restrict__ rotations, const float* __restrict__ opacities,
+                          const float* __restrict__ shs, const float* __restrict__ cov3D_precomp,
+                          const float* __restrict__ colors_precomp, const float* __restrict__ viewmatrix,
+                          const float* __restrict__ projmatrix, const float* __restrict__ campos,
+                          int W, int H, float tanfovx, float tanfovy, float focal_x, float focal_y,
+                          int grid_x, int grid_y, int prefiltered,
+                          int* __restrict__ radii, int* __restrict__ n_touched, GeomState g) {
+    __shared__ float sV[16], sPm[16];
+    __shared__ uint32_t s_warp_sum[kPreBlock / 32];
+    if (threadIdx.x < 16) { sV[threadIdx.x] = viewmatrix[threadIdx.x]; sPm[threadIdx.x] = projmatrix[threadIdx.x]; }
+    __syncthreads();
+    const int idx = blockIdx.x * kPreBlock + threadIdx.x;
+    uint32_t tiles = 0;
+    if (idx < P) {
+        int radius_out = 0;
+        do {
+            const float px = means3D[3 * idx], py = means3D[3 * idx + 1], pz = means3D[3 * idx + 2];
+            // in_frustum (auxiliary.h:139-164): cull on view-space z only
+            const float tz = affine_row_ref(px, py, pz, sV[2], sV[6], sV[10], sV[14]);
+            if (tz <= SPLAT_NEAR) {
+                if (prefiltered) { printf("Point is filtered although prefiltered is set. This shouldn't happen!"); __trap(); }
+                break;
+            }
+            const float tx = affine_row_ref(px, py, pz, sV[0], sV[4], sV[8], sV[12]);
+            const float ty = affine_row_ref(px, py, pz, sV[1], sV[5], sV[9], sV[13]);
+            const float hx = affine_row_ref(px, py, pz, sPm[0], sPm[4], sPm[8], sPm[12]);
+            const float hy = affine_row_ref(px, py, pz, sPm[1], sPm[5], sPm[9], sPm[13]);
+            const float hw = affine_row_ref(px, py, pz, sPm[3], sPm[7], sPm[11], sPm[15]);
+            const float p_w = __frcp_rn(fadd(hw, 0.0000001f));
+            const float projx = fmul(hx, p_w), projy = fmul(hy, p_w);
+            float cov[6];
+            if (cov3D_precomp != nullptr) {
+#pragma unroll
+                for (int k = 0; k < 6; ++k) cov[k] = cov3D_precomp[6 * idx + k];
+            } else {
+                const float4 q = reinterpret_cast<const float4*>(rotations)[idx];
+                cov3d_ref(scales[3 * idx], scales[3 * idx + 1], scales[3 * idx + 2], scale_modifier, q, cov);
+#pragma unroll
+                for (int k = 0; k < 6; ++k) g.cov3D[6 * idx + k] = cov[k];
+            }
+            const float3 abc = cov2d_ref(tx, ty, tz, focal_x, focal_y, tanfovx, tanfovy, cov, sV);
+            // det = a*c - b*b as fma(a, c, -(b*b)); conic = inverse (forward.cu:216-221)
+            const float det = ffma(abc.x, abc.z, -fmul(abc.y, abc.y));
+            if (det == 0.0f) break;
+            const float det_inv = __frcp_rn(det);
+            const float4 con_o = make_float4(fmul(abc.z, det_inv), fmul(-abc.y, det_inv), fmul(abc.x, det_inv),
+                                             opacities[idx]);
+            // radius from the larger eigenvalue (forward.cu:227-231)
+            const float mid = fmul(fadd(abc.x, abc.z), 0.5f);
+            const float sq = __fsqrt_rn(fmaxf(ffma(mid, mid, -det), 0.1f));
+            const float lam = fmaxf(fadd(mid, sq), fsub(mid, sq));
+            const int my_radius = __float2int_ru(fmul(__fsqrt_rn(lam), 3.0f));
+            const float2 pim = make_float2(ndc2pix_ref(projx, W), ndc2pix_ref(projy, H));
+            uint32_t x0, y0, x1, y1;
+            get_rect_ref(pim.x, pim.y, my_radius, grid_x, grid_y, x0, y0, x1, y1);
+            const uint32_t area = (x1 - x0) * (y1 - y0);
+            if (area == 0) break;
+            if (colors_precomp == nullptr) {
+                uint8_t cb;
+                const float3 c = sh_to_rgb(D, M, shs + (size_t)idx * M * 3, make_float3(px, py, pz),
+                                           make_float3(campos[0], campos[1], campos[2]), cb);
+                g.rgb[3 * idx] = c.x; g.rgb[3 * idx + 1] = c.y; g.rgb[3 * idx + 2] = c.z;
+                g.clamped[idx] = cb;
+            }
+            g.depths[idx] = tz;
+            g.means2D[idx] = pim;
+            g.conic_opacity[idx] = con_o;
+            radius_out = my_radius;
+            tiles = area;
+        } while (false);
+        radii[idx] = radius_out;
+        n_touched[idx] = 0;
+        g.tiles_touched[idx] = tiles;
+    }
+    // per-block instance count for the offset scan (replaces half of cub::DeviceScan, rasterizer_impl.cu:280)
+    uint32_t v = tiles;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    if ((threadIdx.x & 31) == 0) s_warp_sum[threadIdx.x >> 5] = v;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint32_t s = 0;
+#pragma unroll
+        for (int w = 0; w < kPreBlock / 32; ++w) s += s_warp_sum[w];
+        g.block_sums[blockIdx.x] = s;
+    }
+}
+
+__global__ void mark_visible_kernel(int P, const float* __restrict__ means3D, const float* __restrict__ viewmatrix,
+                                    bool* __restrict__ present) {
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= P) return;
+    const float tz = affine_row_ref(means3D[3 * idx], means3D[3 * idx + 1], means3D[3 * idx + 2], viewmatrix[2],
+                                    viewmatrix[6], viewmatrix[10], viewmatrix[14]);
+    present[idx] = !(tz <= SPLAT_NEAR);
+}
+
+void launch_preprocess_forward(const FwdParams& p, const GeomState& g, cudaStream_t s) {
+    const int nblk = (p.P + kPreBlock - 1) / kPreBlock;
+    preprocess_forward_kernel<<<nblk, kPreBlock, 0, s>>>(
+        p.P, p.D, p.M, p.means3D, p.scales, p.scale_modifier, p.rotations, p.opacities, p.shs, p.cov3D_precomp,
+        p.colors_precomp, p.viewmatrix, p.projmatrix, p.campos, p.W, p.H, p.tanfovx, p.tanfovy, p.focal_x, p.focal_y,
+        p.grid_x, p.grid_y, p.prefiltered, p.radii, p.n_touched, g);
+}
+
+void launch_mark_visible(int P, const float* means3D, const float* viewmatrix, bool* present, cudaStream_t s) {
+    mark_visible_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, means3D, viewmatrix, present);
+}
+
+}  // namespace splat

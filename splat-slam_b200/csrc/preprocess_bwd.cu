@@ -1,0 +1,290 @@
+// Per-Gaussian backward stage, one pass: conic -> cov2D -> (cov3D, mean, pose), mean2D -> (mean3D, pose),
+// depth -> (mean3D, pose), SH backward, cov3D -> (scale, rotation), plus the block-level reduction of the
+// camera-pose gradient. Fuses DGR/cuda_rasterizer/backward.cu:150-346 (computeCov2DCUDA), :418-539
+// (preprocessCUDA), :21-145 (computeColorFromSH), :350-413 (computeCov3D) and the P x 6 `dL_dtau` reduction
+// that the reference leaves to torch.sum (DGR/diff_gaussian_rasterization/__init__.py:152).
+//
+// Every output row is written exactly once (zeros for culled Gaussians), so none of the ten output tensors
+// needs the zero-fill the reference pays for (rasterize_points.cu:160-170); only the 48-byte packed
+// render-gradient accumulator, which backward render fills with atomics, is cleared beforehand.
+#include "common.cuh"
+#include "kernels.h"
+
+namespace splat {
+
+__device__ const float kB_SH_C0 = 0.28209479177387814f;
+__device__ const float kB_SH_C1 = 0.4886025119029199f;
+__device__ const float kB_SH_C2[5] = {1.0925484305920792f, -1.0925484305920792f, 0.31539156525252005f,
+                                      -1.0925484305920792f, 0.5462742152960396f};
+__device__ const float kB_SH_C3[7] = {-0.5900435899266435f, 2.890611442640554f, -0.4570457994644658f,
+                                      0.3731763325901154f, -0.4570457994644658f, 1.445305721320277f,
+                                      -0.5900435899266435f};
+
+struct f3 { float x, y, z; };
+__device__ __forceinline__ f3 mk(float x, float y, float z) { f3 r; r.x = x; r.y = y; r.z = z; return r; }
+__device__ __forceinline__ f3 operator*(float s, f3 a) { return mk(s * a.x, s * a.y, s * a.z); }
+__device__ __forceinline__ f3 operator+(f3 a, f3 b) { return mk(a.x + b.x, a.y + b.y, a.z + b.z); }
+__device__ __forceinline__ float dot(f3 a, f3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+__device__ __forceinline__ f3 cross(f3 a, f3 b) {
+    return mk(a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x);
+}
+
+// d(normalize(v))/dv applied to dv (auxiliary.h:108-119)
+__device__ __forceinline__ f3 dnormvdv(f3 v, f3 dv) {
+    const float sum2 = v.x * v.x + v.y * v.y + v.z * v.z;
+    const float invsum32 = 1.0f / sqrtf(sum2 * sum2 * sum2);
+    f3 r;
+    r.x = ((+sum2 - v.x * v.x) * dv.x - v.y * v.x * dv.y - v.z * v.x * dv.z) * invsum32;
+    r.y = (-v.x * v.y * dv.x + (sum2 - v.y * v.y) * dv.y - v.z * v.y * dv.z) * invsum32;
+    r.z = (-v.x * v.z * dv.x - v.y * v.z * dv.y + (sum2 - v.z * v.z) * dv.z) * invsum32;
+    return r;
+}
+
+// SH backward (backward.cu:21-145): writes dL_dsh rows [0, M), returns dL/dmean through the view direction.
+__device__ f3 sh_backward(int deg, int M, const float* __restrict__ shs, f3 pos, f3 campos, uint8_t clamp_bits,
+                          f3 dL_dRGB, float* __restrict__ dL_dsh_out) {
+    const f3 dir_orig = mk(pos.x - campos.x, pos.y - campos.y, pos.z - campos.z);
+    const float inv_len = 1.0f / sqrtf(dot(dir_orig, dir_orig));
+    const float x = dir_orig.x * inv_len, y = dir_orig.y * inv_len, z = dir_orig.z * inv_len;
+    const f3* sh = reinterpret_cast<const f3*>(shs);
+    f3* out = reinterpret_cast<f3*>(dL_dsh_out);
+    if (clamp_bits & 1) dL_dRGB.x = 0.0f;
+    if (clamp_bits & 2) dL_dRGB.y = 0.0f;
+    if (clamp_bits & 4) dL_dRGB.z = 0.0f;
+    f3 dRGBdx = mk(0, 0, 0), dRGBdy = mk(0, 0, 0), dRGBdz = mk(0, 0, 0);
+    int written = 1;
+    out[0] = kB_SH_C0 * dL_dRGB;
+    if (deg > 0) {
+        out[1] = (-kB_SH_C1 * y) * dL_dRGB;
+        out[2] = (kB_SH_C1 * z) * dL_dRGB;
+        out[3] = (-kB_SH_C1 * x) * dL_dRGB;
+        written = 4;
+        dRGBdx = (-kB_SH_C1) * sh[3];
+        dRGBdy = (-kB_SH_C1) * sh[1];
+        dRGBdz = kB_SH_C1 * sh[2];
+        if (deg > 1) {
+            const float xx = x * x, yy = y * y, zz = z * z, xy = x * y, yz = y * z, xz = x * z;
+            out[4] = (kB_SH_C2[0] * xy) * dL_dRGB;
+            out[5] = (kB_SH_C2[1] * yz) * dL_dRGB;
+            out[6] = (kB_SH_C2[2] * (2.f * zz - xx - yy)) * dL_dRGB;
+            out[7] = (kB_SH_C2[3] * xz) * dL_dRGB;
+            out[8] = (kB_SH_C2[4] * (xx - yy)) * dL_dRGB;
+            written = 9;
+            dRGBdx = dRGBdx + (kB_SH_C2[0] * y) * sh[4] + (kB_SH_C2[2] * 2.f * -x) * sh[6] + (kB_SH_C2[3] * z) * sh[7] +
+                     (kB_SH_C2[4] * 2.f * x) * sh[8];
+            dRGBdy = dRGBdy + (kB_SH_C2[0] * x) * sh[4] + (kB_SH_C2[1] * z) * sh[5] + (kB_SH_C2[2] * 2.f * -y) * sh[6] +
+                     (kB_SH_C2[4] * 2.f * -y) * sh[8];
+            dRGBdz = dRGBdz + (kB_SH_C2[1] * y) * sh[5] + (kB_SH_C2[2] * 2.f * 2.f * z) * sh[6] + (kB_SH_C2[3] * x) * sh[7];
+            if (deg > 2) {
+                out[9] = (kB_SH_C3[0] * y * (3.f * xx - yy)) * dL_dRGB;
+                out[10] = (kB_SH_C3[1] * xy * z) * dL_dRGB;
+                out[11] = (kB_SH_C3[2] * y * (4.f * zz - xx - yy)) * dL_dRGB;
+                out[12] = (kB_SH_C3[3] * z * (2.f * zz - 3.f * xx - 3.f * yy)) * dL_dRGB;
+                out[13] = (kB_SH_C3[4] * x * (4.f * zz - xx - yy)) * dL_dRGB;
+                out[14] = (kB_SH_C3[5] * z * (xx - yy)) * dL_dRGB;
+                out[15] = (kB_SH_C3[6] * x * (xx - 3.f * yy)) * dL_dRGB;
+                written = 16;
+                dRGBdx = dRGBdx + (kB_SH_C3[0] * 3.f * 2.f * xy) * sh[9] + (kB_SH_C3[1] * yz) * sh[10] +
+                         (kB_SH_C3[2] * -2.f * xy) * sh[11] + (kB_SH_C3[3] * -3.f * 2.f * xz) * sh[12] +
+                         (kB_SH_C3[4] * (-3.f * xx + 4.f * zz - yy)) * sh[13] + (kB_SH_C3[5] * 2.f * xz) * sh[14] +
+                         (kB_SH_C3[6] * 3.f * (xx - yy)) * sh[15];
+                dRGBdy = dRGBdy + (kB_SH_C3[0] * 3.f * (xx - yy)) * sh[9] + (kB_SH_C3[1] * xz) * sh[10] +
+                         (kB_SH_C3[2] * (-3.f * yy + 4.f * zz - xx)) * sh[11] + (kB_SH_C3[3] * -3.f * 2.f * yz) * sh[12] +
+                         (kB_SH_C3[4] * -2.f * xy) * sh[13] + (kB_SH_C3[5] * -2.f * yz) * sh[14] +
+                         (kB_SH_C3[6] * -3.f * 2.f * xy) * sh[15];
+                dRGBdz = dRGBdz + (kB_SH_C3[1] * xy) * sh[10] + (kB_SH_C3[2] * 4.f * 2.f * yz) * sh[11] +
+                         (kB_SH_C3[3] * 3.f * (2.f * zz - xx - yy)) * sh[12] + (kB_SH_C3[4] * 4.f * 2.f * xz) * sh[13] +
+                         (kB_SH_C3[5] * (xx - yy)) * sh[14];
+            }
+        }
+    }
+    for (int k = written; k < M; ++k) out[k] = mk(0, 0, 0);
+    const f3 dL_ddir = mk(dot(dRGBdx, dL_dRGB), dot(dRGBdy, dL_dRGB), dot(dRGBdz, dL_dRGB));
+    return dnormvdv(dir_orig, dL_ddir);
+}
+
+__global__ void __launch_bounds__(kPreBlock)
+preprocess_backward_kernel(BwdParams p, GeomState g, float* __restrict__ tau_partial) {
+    __shared__ float sV[16], sPm[16];
+    __shared__ float s_tau[kPreBlock / 32][6];
+    if (threadIdx.x < 16) { sV[threadIdx.x] = p.viewmatrix[threadIdx.x]; sPm[threadIdx.x] = p.projmatrix[threadIdx.x]; }
+    __syncthreads();
+    const int idx = blockIdx.x * kPreBlock + threadIdx.x;
+    float tau[6] = {0, 0, 0, 0, 0, 0};
+    if (idx < p.P) {
+        const bool vis = p.radii[idx] > 0;
+        f3 dmean = mk(0, 0, 0);
+        float dcov[6] = {0, 0, 0, 0, 0, 0};
+        float4 acc0 = make_float4(0, 0, 0, 0), acc1 = acc0, acc2 = acc0;
+        if (vis) {
+            const float4* acc = reinterpret_cast<const float4*>(p.grad_accum) + 3 * (size_t)idx;
+            acc0 = acc[0];   // mean2D.x, mean2D.y, conic.x, conic.y
+            acc1 = acc[1];   // conic.w, opacity, r, g
+            acc2 = acc[2];   // b, depth, -, -
+            const f3 m = mk(p.means3D[3 * idx], p.means3D[3 * idx + 1], p.means3D[3 * idx + 2]);
+            const float* cov3D = p.cov3D_precomp ? p.cov3D_precomp + 6 * (size_t)idx : g.cov3D + 6 * (size_t)idx;
+
+            // ---------------- conic -> cov2D -> cov3D / t / W  (backward.cu:150-346) ----------------
+            f3 t = mk(sV[0] * m.x + sV[4] * m.y + sV[8] * m.z + sV[12], sV[1] * m.x + sV[5] * m.y + sV[9] * m.z + sV[13],
+                      sV[2] * m.x + sV[6] * m.y + sV[10] * m.z + sV[14]);
+            const f3 p_C = t;   // unclamped camera-frame point, used by the mean2D/depth pose terms below
+            const float limx = 1.3f * p.tanfovx, limy = 1.3f * p.tanfovy;
+            const float txtz = t.x / t.z, tytz = t.y / t.z;
+            t.x = fminf(limx, fmaxf(-limx, txtz)) * t.z;
+            t.y = fminf(limy, fmaxf(-limy, tytz)) * t.z;
+            const float x_grad_mul = (txtz < -limx || txtz > limx) ? 0.0f : 1.0f;
+            const float y_grad_mul = (tytz < -limy || tytz > limy) ? 0.0f : 1.0f;
+            const float hx = p.focal_x, hy = p.focal_y;
+            const float J00 = hx / t.z, J02 = -(hx * t.x) / (t.z * t.z);
+            const float J11 = hy / t.z, J12 = -(hy * t.y) / (t.z * t.z);
+            // rows of the world->camera rotation: R(i,k) = view[4k+i]
+            const f3 R0 = mk(sV[0], sV[4], sV[8]), R1 = mk(sV[1], sV[5], sV[9]), R2 = mk(sV[2], sV[6], sV[10]);
+            const f3 A0 = J00 * R0 + J02 * R2;     // A = J R, rows 0 and 1
+            const f3 A1 = J11 * R1 + J12 * R2;
+            const f3 V0 = mk(cov3D[0], cov3D[1], cov3D[2]), V1 = mk(cov3D[1], cov3D[3], cov3D[4]),
+                     V2 = mk(cov3D[2], cov3D[4], cov3D[5]);
+            const f3 VA0 = mk(dot(V0, A0), dot(V1, A0), dot(V2, A0));
+            const f3 VA1 = mk(dot(V0, A1), dot(V1, A1), dot(V2, A1));
+            const float a = dot(A0, VA0) + 0.3f, b = dot(A0, VA1), c = dot(A1, VA1) + 0.3f;
+            const float denom = a * c - b * b;
+            const float denom2inv = 1.0f / ((denom * denom) + 0.0000001f);
+            const float gx = acc0.z, gy = acc0.w, gz = acc1.x;   // dL_dconic slots [0],[1],[3]
+            float dL_da = 0, dL_db = 0, dL_dc = 0;
+            if (denom2inv != 0.0f) {
+                dL_da = denom2inv * (-c * c * gx + 2 * b * c * gy + (denom - a * c) * gz);
+                dL_dc = denom2inv * (-a * a * gz + 2 * a * b * gy + (denom - a * c) * gx);
+                dL_db = denom2inv * 2 * (b * c * gx - (denom + 2 * b * b) * gy + a * b * gz);
+                dcov[0] = A0.x * A0.x * dL_da + A0.x * A1.x * dL_db + A1.x * A1.x * dL_dc;
+                dcov[3] = A0.y * A0.y * dL_da + A0.y * A1.y * dL_db + A1.y * A1.y * dL_dc;
+                dcov[5] = A0.z * A0.z * dL_da + A0.z * A1.z * dL_db + A1.z * A1.z * dL_dc;
+                dcov[1] = 2 * A0.x * A0.y * dL_da + (A0.x * A1.y + A0.y * A1.x) * dL_db + 2 * A1.x * A1.y * dL_dc;
+                dcov[2] = 2 * A0.x * A0.z * dL_da + (A0.x * A1.z + A0.z * A1.x) * dL_db + 2 * A1.x * A1.z * dL_dc;
+                dcov[4] = 2 * A0.z * A0.y * dL_da + (A0.y * A1.z + A0.z * A1.y) * dL_db + 2 * A1.y * A1.z * dL_dc;
+            }
+            const f3 dA0 = (2 * dL_da) * VA0 + dL_db * VA1;    // dL/dA(0,:)
+            const f3 dA1 = (2 * dL_dc) * VA1 + dL_db * VA0;    // dL/dA(1,:)
+            const float dJ00 = dot(R0, dA0), dJ02 = dot(R2, dA0), dJ11 = dot(R1, dA1), dJ12 = dot(R2, dA1);
+            const float tz = 1.0f / t.z, tz2 = tz * tz, tz3 = tz2 * tz;
+            const f3 dt = mk(x_grad_mul * -hx * tz2 * dJ02, y_grad_mul * -hy * tz2 * dJ12,
+                             -hx * tz2 * dJ00 - hy * tz2 * dJ11 + (2 * hx * t.x) * tz3 * dJ02 + (2 * hy * t.y) * tz3 * dJ12);
+            // pose: d p_C / d rho = I, d p_C / d theta = -skew(t) with the CLAMPED t (backward.cu:273-288)
+            const f3 th_t = cross(t, dt);
+            tau[0] += dt.x; tau[1] += dt.y; tau[2] += dt.z;
+            tau[3] += th_t.x; tau[4] += th_t.y; tau[5] += th_t.z;
+            // mean through t: R^T dt (backward.cu:292-297)
+            dmean = mk(sV[0] * dt.x + sV[1] * dt.y + sV[2] * dt.z, sV[4] * dt.x + sV[5] * dt.y + sV[6] * dt.z,
+                       sV[8] * dt.x + sV[9] * dt.y + sV[10] * dt.z);
+            // rotation columns through W (backward.cu:299-343): theta += sum_k col_k(R) x dL/dR(:,k)
+            const f3 dW0 = J00 * dA0, dW1 = J11 * dA1, dW2 = J02 * dA0 + J12 * dA1;   // rows m of dL/dR(m, k)
+            {
+                const f3 c0 = mk(sV[0], sV[1], sV[2]), c1 = mk(sV[4], sV[5], sV[6]), c2 = mk(sV[8], sV[9], sV[10]);
+                const f3 w0 = cross(c0, mk(dW0.x, dW1.x, dW2.x));
+                const f3 w1 = cross(c1, mk(dW0.y, dW1.y, dW2.y));
+                const f3 w2 = cross(c2, mk(dW0.z, dW1.z, dW2.z));
+                tau[3] += w0.x + w1.x + w2.x; tau[4] += w0.y + w1.y + w2.y; tau[5] += w0.z + w1.z + w2.z;
+            }
+
+            // ---------------- mean2D -> mean3D / pose (backward.cu:446-512) ----------------
+            const float m_hx = sPm[0] * m.x + sPm[4] * m.y + sPm[8] * m.z + sPm[12];
+            const float m_hy = sPm[1] * m.x + sPm[5] * m.y + sPm[9] * m.z + sPm[13];
+            const float m_hw = sPm[3] * m.x + sPm[7] * m.y + sPm[11] * m.z + sPm[15];
+            const float m_w = 1.0f / (m_hw + 0.0000001f);
+            const float mul1 = m_hx * m_w * m_w, mul2 = m_hy * m_w * m_w;
+            const float g2x = acc0.x, g2y = acc0.y;
+            dmean.x += (sPm[0] * m_w - sPm[3] * mul1) * g2x + (sPm[1] * m_w - sPm[3] * mul2) * g2y;
+            dmean.y += (sPm[4] * m_w - sPm[7] * mul1) * g2x + (sPm[5] * m_w - sPm[7] * mul2) * g2y;
+            dmean.z += (sPm[8] * m_w - sPm[11] * mul1) * g2x + (sPm[9] * m_w - sPm[11] * mul2) * g2y;
+            {
+                const float alpha = m_w, beta = -m_hx * m_w * m_w, gamma = -m_hy * m_w * m_w;
+                const float pa = p.projmatrix_raw[0], pb = p.projmatrix_raw[5], pe = p.projmatrix_raw[11];
+                const f3 v1 = mk(alpha * pa, 0.0f, beta * pe), v2 = mk(0.0f, alpha * pb, gamma * pe);
+                const f3 th1 = cross(p_C, v1), th2 = cross(p_C, v2);
+                tau[0] += g2x * v1.x + g2y * v2.x; tau[1] += g2x * v1.y + g2y * v2.y; tau[2] += g2x * v1.z + g2y * v2.z;
+                tau[3] += g2x * th1.x + g2y * th2.x; tau[4] += g2x * th1.y + g2y * th2.y; tau[5] += g2x * th1.z + g2y * th2.z;
+            }
+            // ---------------- depth -> mean3D / pose (backward.cu:514-528) ----------------
+            const float gd = acc2.y;
+            dmean.x += gd * sV[2]; dmean.y += gd * sV[6]; dmean.z += gd * sV[10];
+            tau[2] += gd; tau[3] += gd * p_C.y; tau[4] += -gd * p_C.x;
+
+            // ---------------- SH (backward.cu:532-534) ----------------
+            if (p.shs != nullptr) {
+                const f3 dm = sh_backward(p.D, p.M, p.shs + (size_t)idx * p.M * 3, m,
+                                          mk(p.campos[0], p.campos[1], p.campos[2]), g.clamped[idx],
+                                          mk(acc1.z, acc1.w, acc2.x), p.dL_dsh + (size_t)idx * p.M * 3);
+                dmean = dmean + dm;
+                tau[0] -= dm.x; tau[1] -= dm.y; tau[2] -= dm.z;
+            }
+            // ---------------- cov3D -> scale / rotation (backward.cu:350-413) ----------------
+            if (p.scales != nullptr) {
+                const float4 q4 = reinterpret_cast<const float4*>(p.rotations)[idx];
+                const float r = q4.x, x = q4.y, y = q4.z, z = q4.w;
+                // rows of Rq; glm's R has them as columns, M = S * R  ->  M(col c) = s (.) Rq-row c
+                const f3 q0 = mk(1.f - 2.f * (y * y + z * z), 2.f * (x * y - r * z), 2.f * (x * z + r * y));
+                const f3 q1 = mk(2.f * (x * y + r * z), 1.f - 2.f * (x * x + z * z), 2.f * (y * z - r * x));
+                const f3 q2 = mk(2.f * (x * z - r * y), 2.f * (y * z + r * x), 1.f - 2.f * (x * x + y * y));
+                const f3 s = mk(p.scale_modifier * p.scales[3 * idx], p.scale_modifier * p.scales[3 * idx + 1],
+                                p.scale_modifier * p.scales[3 * idx + 2]);
+                // symmetric dL/dSigma with halved off-diagonals
+                const f3 S0 = mk(dcov[0], 0.5f * dcov[1], 0.5f * dcov[2]), S1 = mk(0.5f * dcov[1], dcov[3], 0.5f * dcov[4]),
+                         S2 = mk(0.5f * dcov[2], 0.5f * dcov[4], dcov[5]);
+                // Sigma_ij = sum_k s_k^2 Rq(i,k) Rq(j,k). With G = dL/dSigma (symmetric):
+                //   dL/ds_k = 2 s_k * sum_ij G_ij Rq(i,k) Rq(j,k);  dL/dRq(i,k) = 2 s_k^2 * sum_j G_ij Rq(j,k)
+                const f3 col0 = mk(q0.x, q1.x, q2.x), col1 = mk(q0.y, q1.y, q2.y), col2 = mk(q0.z, q1.z, q2.z);
+                const f3 Gc0 = mk(dot(S0, col0), dot(S1, col0), dot(S2, col0));
+                const f3 Gc1 = mk(dot(S0, col1), dot(S1, col1), dot(S2, col1));
+                const f3 Gc2 = mk(dot(S0, col2), dot(S1, col2), dot(S2, col2));
+                p.dL_dscale[3 * idx] = 2.f * s.x * dot(col0, Gc0);
+                p.dL_dscale[3 * idx + 1] = 2.f * s.y * dot(col1, Gc1);
+                p.dL_dscale[3 * idx + 2] = 2.f * s.z * dot(col2, Gc2);
+                // dL/dRq(i,k): D[i][k]
+                const f3 D0 = mk(2.f * s.x * s.x * Gc0.x, 2.f * s.y * s.y * Gc1.x, 2.f * s.z * s.z * Gc2.x);
+                const f3 D1 = mk(2.f * s.x * s.x * Gc0.y, 2.f * s.y * s.y * Gc1.y, 2.f * s.z * s.z * Gc2.y);
+                const f3 D2 = mk(2.f * s.x * s.x * Gc0.z, 2.f * s.y * s.y * Gc1.z, 2.f * s.z * s.z * Gc2.z);
+                // chain through Rq(q) for the raw quaternion (no normalisation Jacobian, backward.cu:410-412)
+                float4 dq;
+                dq.x = 2.f * (-z * D0.y + y * D0.z + z * D1.x - x * D1.z - y * D2.x + x * D2.y);
+                dq.y = 2.f * (y * D0.y + z * D0.z + y * D1.x - 2.f * x * D1.y - r * D1.z + z * D2.x + r * D2.y - 2.f * x * D2.z);
+                dq.z = 2.f * (-2.f * y * D0.x + x * D0.y + r * D0.z + x * D1.x + z * D1.z - r * D2.x + z * D2.y - 2.f * y * D2.z);
+                dq.w = 2.f * (-2.f * z * D0.x - r * D0.y + x * D0.z + r * D1.x - 2.f * z * D1.y + y * D1.z + x * D2.x + y * D2.y);
+                reinterpret_cast<float4*>(p.dL_drot)[idx] = dq;
+            }
+        } else {
+            if (p.shs != nullptr)
+                for (int k = 0; k < p.M * 3; ++k) p.dL_dsh[(size_t)idx * p.M * 3 + k] = 0.0f;
+            if (p.scales != nullptr) {
+                p.dL_dscale[3 * idx] = 0.0f; p.dL_dscale[3 * idx + 1] = 0.0f; p.dL_dscale[3 * idx + 2] = 0.0f;
+                reinterpret_cast<float4*>(p.dL_drot)[idx] = make_float4(0, 0, 0, 0);
+            }
+        }
+        p.dL_dmean2D[3 * idx] = acc0.x; p.dL_dmean2D[3 * idx + 1] = acc0.y; p.dL_dmean2D[3 * idx + 2] = 0.0f;
+        p.dL_dopacity[idx] = acc1.y;
+        p.dL_dcolors[3 * idx] = acc1.z; p.dL_dcolors[3 * idx + 1] = acc1.w; p.dL_dcolors[3 * idx + 2] = acc2.x;
+        p.dL_dmean3D[3 * idx] = dmean.x; p.dL_dmean3D[3 * idx + 1] = dmean.y; p.dL_dmean3D[3 * idx + 2] = dmean.z;
+#pragma unroll
+        for (int k = 0; k < 6; ++k) p.dL_dcov3D[6 * (size_t)idx + k] = dcov[k];
+    }
+    // camera-pose gradient: block-reduce the six components, one partial row per block
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+    for (int k = 0; k < 6; ++k) {
+        float v = tau[k];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        if (lane == 0) s_tau[warp][k] = v;
+    }
+    __syncthreads();
+    if (threadIdx.x < 6) {
+        float s = 0.0f;
+#pragma unroll
+        for (int w = 0; w < kPreBlock / 32; ++w) s += s_tau[w][threadIdx.x];
+        tau_partial[6 * (size_t)blockIdx.x + threadIdx.x] = s;
+    }
+}
+
+void launch_preprocess_backward(const BwdParams& p, const GeomState& g, cudaStream_t s) {
+    const int nblk = (p.P + kPreBlock - 1) / kPreBlock;
+    preprocess_backward_kernel<<<nblk, kPreBlock, 0, s>>>(p, g, p.dL_dtau);
+}
+
+}  // namespace splat

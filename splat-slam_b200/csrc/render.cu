@@ -1,0 +1,353 @@
+// Tile renderers: forward front-to-back alpha compositing of colour/depth/opacity and the backward pass with
+// back-to-front recomposition. Replaces DGR/cuda_rasterizer/forward.cu:263-392 and backward.cu:541-787.
+//
+// B200 design: one CTA per 16x16 tile (tile ids/ranges stay bit-compatible with the reference). Each warp owns
+// an 8x4 pixel patch so whole-warp rejection of a Gaussian is likely. Per-instance 48-byte records (built in
+// sorted order by ranges_and_records_kernel) are streamed into a two-stage shared-memory ring with
+// cp.async.bulk (TMA 1-D bulk copy, SASS UBLKCP) completing on an mbarrier; the consumer loop reads them with
+// broadcast LDS.128. The backward reduces the 10 per-Gaussian gradient terms across the warp with a
+// recursive-halving shuffle tree (12 SHFL instead of 50) and issues one RED per term per warp.
+#include "common.cuh"
+#include "kernels.h"
+
+namespace splat {
+
+constexpr int kBatch = 128;                              // records per pipeline stage
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void fence_mbar_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+// one thread: arm the barrier with the byte count and launch the bulk copy global -> shared
+__device__ __forceinline__ void bulk_load(void* dst_smem, const void* src_gmem, uint32_t bytes, uint64_t* bar) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     smem_u32(dst_smem)),
+                 "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    uint32_t ok;
+    do {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(ok)
+            : "r"(smem_u32(bar)), "r"(parity)
+            : "memory");
+    } while (!ok);
+}
+
+// pixel owned by (warp, lane): warps tile the 16x16 block as 2 x 4 patches of 8 x 4 pixels
+__device__ __forceinline__ void pixel_of_thread(int tile_x, int tile_y, uint32_t& px, uint32_t& py) {
+    const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    px = tile_x * SPLAT_TILE + (warp & 1) * 8 + (lane & 7);
+    py = tile_y * SPLAT_TILE + (warp >> 1) * 4 + (lane >> 3);
+}
+
+// =====================================================================================================
+// forward
+// =====================================================================================================
+__global__ void __launch_bounds__(SPLAT_TILE_PIXELS)
+render_forward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ranges, const float* __restrict__ records,
+                      const float* __restrict__ bg, float* __restrict__ final_T, uint32_t* __restrict__ n_contrib,
+                      float* __restrict__ out_color, float* __restrict__ out_depth, float* __restrict__ out_opacity,
+                      int* __restrict__ n_touched) {
+    __shared__ __align__(128) float4 s_rec[2][kBatch * 3];
+    __shared__ __align__(8) uint64_t s_bar[2];
+    __shared__ int s_cnt[2][kBatch];
+
+    const int tile = blockIdx.x;
+    const int tile_x = tile % grid_x, tile_y = tile / grid_x;
+    uint32_t px, py;
+    pixel_of_thread(tile_x, tile_y, px, py);
+    const bool inside = px < (uint32_t)W && py < (uint32_t)H;
+    const uint32_t pix_id = (uint32_t)W * py + px;
+    const float pixfx = (float)px, pixfy = (float)py;
+    const uint32_t lane = threadIdx.x & 31;
+
+    const uint2 range = ranges[tile];
+    const int n = (int)(range.y - range.x);
+    const int nb = (n + kBatch - 1) / kBatch;
+    const float4* src = reinterpret_cast<const float4*>(records) + 3 * (size_t)range.x;
+
+    if (threadIdx.x == 0) { mbar_init(&s_bar[0], 1); mbar_init(&s_bar[1], 1); fence_mbar_init(); }
+    if (threadIdx.x < kBatch) { s_cnt[0][threadIdx.x] = 0; s_cnt[1][threadIdx.x] = 0; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int b = 0; b < 2 && b < nb; ++b) {
+            const int cnt = min(kBatch, n - b * kBatch);
+            bulk_load(&s_rec[b][0], src + 3 * (size_t)b * kBatch, (uint32_t)cnt * 48u, &s_bar[b]);
+        }
+    }
+
+    bool done = !inside;
+    float T = 1.0f, C0 = 0.0f, C1 = 0.0f, C2 = 0.0f, Dp = 0.0f;
+    uint32_t last_contributor = 0;
+
+    int b = 0;
+    for (; b < nb; ++b) {
+        // whole tile saturated -> stop (forward.cu:318-320)
+        if (__syncthreads_count(done) == SPLAT_TILE_PIXELS) break;
+        const int stage = b & 1;
+        const int cnt = min(kBatch, n - b * kBatch);
+        mbar_wait(&s_bar[stage], (uint32_t)((b >> 1) & 1));
+        const float4* rec = &s_rec[stage][0];
+        for (int j = 0; j < cnt; ++j) {
+            if (__all_sync(0xffffffffu, done)) break;
+            const float4 r0 = rec[3 * j];          // x, y, conic.x, conic.y
+            const float4 r1 = rec[3 * j + 1];      // conic.z, opacity, depth, id
+            const float dx = fsub(r0.x, pixfx), dy = fsub(r0.y, pixfy);
+            const float power = gauss_power_ref(dx, dy, r0.z, r0.w, r1.x);
+            bool act = !done && !(power > 0.0f);
+            if (!__any_sync(0xffffffffu, act)) continue;
+            // alpha = min(0.99, opacity * exp(power)); 1/255 cut; transmittance test (forward.cu:350-363)
+            const float alpha = fminf(0.99f, fmul(r1.y, expf(power)));
+            act = act && !(alpha < 1.0f / 255.0f);
+            const float test_T = fmul(T, fsub(1.0f, alpha));
+            if (act && test_T < 0.0001f) { done = true; act = false; }
+            if (__any_sync(0xffffffffu, act)) {
+                const float4 r2 = rec[3 * j + 2];  // r, g, b
+                if (act) {
+                    // C += c * alpha * T as fma(T, alpha*c, C) (reference SASS order)
+                    C0 = ffma(T, fmul(alpha, r2.x), C0);
+                    C1 = ffma(T, fmul(alpha, r2.y), C1);
+                    C2 = ffma(T, fmul(alpha, r2.z), C2);
+                    Dp = ffma(T, fmul(alpha, r1.z), Dp);
+                    T = test_T;
+                    last_contributor = (uint32_t)(b * kBatch + j + 1);
+                }
+                // n_touched: pixels that blended this Gaussian while still > 50 % transparent (forward.cu:368-370)
+                const uint32_t tv = __ballot_sync(0xffffffffu, act && test_T > 0.5f);
+                if (tv != 0u && lane == 0) atomicAdd(&s_cnt[stage][j], __popc(tv));
+            }
+        }
+        __syncthreads();   // every warp is done with this stage
+        if (threadIdx.x < cnt) {
+            const int c = s_cnt[stage][threadIdx.x];
+            if (c) {
+                atomicAdd(&n_touched[__float_as_int(rec[3 * threadIdx.x + 1].w)], c);
+                s_cnt[stage][threadIdx.x] = 0;
+            }
+        }
+        __syncthreads();   // ids read before the stage is overwritten
+        if (threadIdx.x == 0 && b + 2 < nb) {
+            const int cnt2 = min(kBatch, n - (b + 2) * kBatch);
+            fence_proxy_async();
+            bulk_load(&s_rec[stage][0], src + 3 * (size_t)(b + 2) * kBatch, (uint32_t)cnt2 * 48u, &s_bar[stage]);
+        }
+    }
+
+    // an early stop leaves up to two bulk copies in flight: they must land before this CTA's shared memory
+    // can be handed to another CTA
+    if (threadIdx.x == 0) {
+        for (int k = b; k < nb && k < b + 2; ++k) mbar_wait(&s_bar[k & 1], (uint32_t)((k >> 1) & 1));
+    }
+
+    if (inside) {
+        final_T[pix_id] = T;
+        n_contrib[pix_id] = last_contributor;
+        const size_t HW = (size_t)H * W;
+        out_color[pix_id] = ffma(bg[0], T, C0);
+        out_color[HW + pix_id] = ffma(bg[1], T, C1);
+        out_color[2 * HW + pix_id] = ffma(bg[2], T, C2);
+        out_depth[pix_id] = Dp;
+        out_opacity[pix_id] = fsub(1.0f, T);
+    }
+}
+
+void launch_render_forward(int W, int H, int grid_x, int grid_y, const uint2* ranges, const float* records,
+                           const float* bg, float* final_T, uint32_t* n_contrib, float* out_color, float* out_depth,
+                           float* out_opacity, int* n_touched, cudaStream_t s) {
+    render_forward_kernel<<<grid_x * grid_y, SPLAT_TILE_PIXELS, 0, s>>>(W, H, grid_x, ranges, records, bg, final_T,
+                                                                        n_contrib, out_color, out_depth, out_opacity,
+                                                                        n_touched);
+}
+
+// =====================================================================================================
+// backward
+// =====================================================================================================
+// Recursive-halving all-lane reduction of 10 values: after the five exchange rounds the lane with
+// bit0 == 0 and index k = 5*bit4 + 3*bit3 + 2*bit2 + bit1 (when valid) holds the warp total of value k.
+__device__ __forceinline__ float warp_reduce10(const float (&v)[10], uint32_t lane) {
+    const bool h16 = lane & 16, h8 = lane & 8, h4 = lane & 4, h2 = lane & 2;
+    float a[5];
+#pragma unroll
+    for (int k = 0; k < 5; ++k) {
+        const float send = h16 ? v[k] : v[k + 5];
+        const float keep = h16 ? v[k + 5] : v[k];
+        a[k] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
+    }
+    float b[3];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        const float hi = (k + 3 < 5) ? a[k + 3] : 0.0f;
+        const float send = h8 ? a[k] : hi;
+        const float keep = h8 ? hi : a[k];
+        b[k] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
+    }
+    float c[2];
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+        const float hi = (k + 2 < 3) ? b[k + 2] : 0.0f;
+        const float send = h4 ? b[k] : hi;
+        const float keep = h4 ? hi : b[k];
+        c[k] = keep + __shfl_xor_sync(0xffffffffu, send, 4);
+    }
+    float d;
+    {
+        const float send = h2 ? c[0] : c[1];
+        const float keep = h2 ? c[1] : c[0];
+        d = keep + __shfl_xor_sync(0xffffffffu, send, 2);
+    }
+    d += __shfl_xor_sync(0xffffffffu, d, 1);
+    return d;
+}
+
+__global__ void __launch_bounds__(SPLAT_TILE_PIXELS)
+render_backward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ranges, const float* __restrict__ records,
+                       const float* __restrict__ bg, const float* __restrict__ final_Ts,
+                       const uint32_t* __restrict__ n_contrib, const float* __restrict__ dL_dpixels,
+                       const float* __restrict__ dL_dpixels_depth, float* __restrict__ grad_accum) {
+    __shared__ __align__(128) float4 s_rec[2][kBatch * 3];
+    __shared__ __align__(8) uint64_t s_bar[2];
+
+    const int tile = blockIdx.x;
+    const int tile_x = tile % grid_x, tile_y = tile / grid_x;
+    uint32_t px, py;
+    pixel_of_thread(tile_x, tile_y, px, py);
+    const bool inside = px < (uint32_t)W && py < (uint32_t)H;
+    const uint32_t pix_id = (uint32_t)W * py + px;
+    const float pixfx = (float)px, pixfy = (float)py;
+    const uint32_t lane = threadIdx.x & 31;
+
+    const uint2 range = ranges[tile];
+    const int n = (int)(range.y - range.x);
+    const int nb = (n + kBatch - 1) / kBatch;
+    const float4* src = reinterpret_cast<const float4*>(records) + 3 * (size_t)range.x;
+
+    // batch b (counted from the BACK of the list) covers list indices [lo_b, hi_b)
+    auto batch_lo = [&](int b) { return max(0, n - (b + 1) * kBatch); };
+    auto batch_hi = [&](int b) { return n - b * kBatch; };
+
+    if (threadIdx.x == 0) { mbar_init(&s_bar[0], 1); mbar_init(&s_bar[1], 1); fence_mbar_init(); }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int b = 0; b < 2 && b < nb; ++b) {
+            const int lo = batch_lo(b), cnt = batch_hi(b) - lo;
+            bulk_load(&s_rec[b][0], src + 3 * (size_t)lo, (uint32_t)cnt * 48u, &s_bar[b]);
+        }
+    }
+
+    // which of the 10 reduced terms this lane ends up holding (see warp_reduce10), and where it goes in the
+    // packed accumulator {mean2D.x, mean2D.y, conic.x, conic.y, conic.w, opacity, r, g, b, depth, -, -}
+    const int inner3 = ((lane >> 2) & 1) * 2 + ((lane >> 1) & 1);
+    const int inner5 = ((lane >> 3) & 1) * 3 + inner3;
+    const int my_k = ((lane >> 4) & 1) * 5 + inner5;
+    const bool holder = ((lane & 1) == 0) && inner3 < 3 && inner5 < 5;
+
+    const float T_final = inside ? final_Ts[pix_id] : 0.0f;
+    float T = T_final;
+    const int last_contributor = inside ? (int)n_contrib[pix_id] : 0;
+    const size_t HW = (size_t)H * W;
+    float dLp0 = 0.0f, dLp1 = 0.0f, dLp2 = 0.0f, dLpd = 0.0f;
+    if (inside) {
+        dLp0 = dL_dpixels[pix_id]; dLp1 = dL_dpixels[HW + pix_id]; dLp2 = dL_dpixels[2 * HW + pix_id];
+        dLpd = dL_dpixels_depth[pix_id];
+    }
+    const float bg_dot_dpixel = bg[0] * dLp0 + bg[1] * dLp1 + bg[2] * dLp2;
+    float acc0 = 0.0f, acc1 = 0.0f, acc2 = 0.0f, accd = 0.0f;         // accum_rec, accum_rec_depth
+    float last_alpha = 0.0f, lc0 = 0.0f, lc1 = 0.0f, lc2 = 0.0f, last_depth = 0.0f;
+    const float ddelx_dx = 0.5f * W, ddely_dy = 0.5f * H;               // backward.cu:643-644
+
+    // nothing in this warp ever blended anything -> the warp only helps with barriers
+    const int warp_last = __reduce_max_sync(0xffffffffu, last_contributor);
+
+    for (int b = 0; b < nb; ++b) {
+        const int stage = b & 1;
+        const int lo = batch_lo(b), cnt = batch_hi(b) - lo;
+        mbar_wait(&s_bar[stage], (uint32_t)((b >> 1) & 1));
+        const float4* rec = &s_rec[stage][0];
+        if (lo < warp_last) {
+            for (int j = min(cnt, warp_last - lo) - 1; j >= 0; --j) {
+                const int idx = lo + j;                        // position in the tile's list
+                const float4 r0 = rec[3 * j];
+                const float4 r1 = rec[3 * j + 1];
+                const float dx = fsub(r0.x, pixfx), dy = fsub(r0.y, pixfy);
+                const float power = gauss_power_ref(dx, dy, r0.z, r0.w, r1.x);
+                bool skip = (idx >= last_contributor) || (power > 0.0f);
+                if (__all_sync(0xffffffffu, skip)) continue;
+                const float G = expf(power);
+                const float alpha = fminf(0.99f, fmul(r1.y, G));
+                skip = skip || (alpha < 1.0f / 255.0f);
+                if (__all_sync(0xffffffffu, skip)) continue;
+                const float4 r2 = rec[3 * j + 2];
+
+                const float one_m_alpha = 1.0f - alpha;
+                const float inv = __frcp_rn(one_m_alpha);
+                T = skip ? T : T * inv;
+                const float dchannel_dcolor = alpha * T;
+                float dL_dalpha;
+                {
+                    const float na0 = last_alpha * lc0 + (1.0f - last_alpha) * acc0;
+                    const float na1 = last_alpha * lc1 + (1.0f - last_alpha) * acc1;
+                    const float na2 = last_alpha * lc2 + (1.0f - last_alpha) * acc2;
+                    const float nad = last_alpha * last_depth + (1.0f - last_alpha) * accd;
+                    acc0 = skip ? acc0 : na0; acc1 = skip ? acc1 : na1; acc2 = skip ? acc2 : na2;
+                    accd = skip ? accd : nad;
+                    lc0 = skip ? lc0 : r2.x; lc1 = skip ? lc1 : r2.y; lc2 = skip ? lc2 : r2.z;
+                    last_depth = skip ? last_depth : r1.z;
+                    dL_dalpha = (r2.x - acc0) * dLp0 + (r2.y - acc1) * dLp1 + (r2.z - acc2) * dLp2 +
+                                (r1.z - accd) * dLpd;
+                }
+                dL_dalpha *= T;
+                last_alpha = skip ? last_alpha : alpha;
+                // alpha also scales how much background shows through (backward.cu:736-743)
+                dL_dalpha += (-T_final * inv) * bg_dot_dpixel;
+
+                const float dL_dG = r1.y * dL_dalpha;
+                const float gdx = G * dx, gdy = G * dy;
+                const float dG_ddelx = -gdx * r0.z - gdy * r0.w;
+                const float dG_ddely = -gdy * r1.x - gdx * r0.w;
+                float v[10];
+                v[0] = dL_dG * dG_ddelx * ddelx_dx;
+                v[1] = dL_dG * dG_ddely * ddely_dy;
+                v[2] = -0.5f * gdx * dx * dL_dG;
+                v[3] = -0.5f * gdx * dy * dL_dG;
+                v[4] = -0.5f * gdy * dy * dL_dG;
+                v[5] = G * dL_dalpha;
+                v[6] = dchannel_dcolor * dLp0;
+                v[7] = dchannel_dcolor * dLp1;
+                v[8] = dchannel_dcolor * dLp2;
+                v[9] = dchannel_dcolor * dLpd;
+#pragma unroll
+                for (int k = 0; k < 10; ++k) v[k] = skip ? 0.0f : v[k];
+                const float total = warp_reduce10(v, lane);
+                if (holder && total != 0.0f) {
+                    const uint32_t id = __float_as_uint(r1.w);
+                    atomicAdd(&grad_accum[(size_t)id * SPLAT_GRAD_FLOATS + my_k], total);
+                }
+            }
+        }
+        __syncthreads();
+        if (threadIdx.x == 0 && b + 2 < nb) {
+            const int lo2 = batch_lo(b + 2), cnt2 = batch_hi(b + 2) - lo2;
+            fence_proxy_async();
+            bulk_load(&s_rec[stage][0], src + 3 * (size_t)lo2, (uint32_t)cnt2 * 48u, &s_bar[stage]);
+        }
+    }
+}
+
+void launch_render_backward(int W, int H, int grid_x, int grid_y, const uint2* ranges, const float* records,
+                            const float* bg, const float* final_T, const uint32_t* n_contrib, const float* dL_dpix,
+                            const float* dL_dpix_depth, float* grad_accum, cudaStream_t s) {
+    render_backward_kernel<<<grid_x * grid_y, SPLAT_TILE_PIXELS, 0, s>>>(W, H, grid_x, ranges, records, bg, final_T,
+                                                                         n_contrib, dL_dpix, dL_dpix_depth, grad_accum);
+}
+
+}  // namespace splat

@@ -1,0 +1,282 @@
+"""Drop-in `diff_gaussian_rasterization` for Splat-SLAM, backed by hand-written sm_100a CUDA.
+
+Public surface and semantics mirror the reference package
+(thirdparty/diff-gaussian-rasterization-w-pose/diff_gaussian_rasterization/__init__.py, "DGR" below):
+
+  * `GaussianRasterizationSettings`  — the 13-field NamedTuple (DGR __init__.py:173-186)
+  * `GaussianRasterizer(raster_settings)(means3D, means2D, opacities, shs, colors_precomp, scales, rotations,
+     cov3D_precomp, theta, rho)` -> `(color, radii, depth, opacity, n_touched)` (DGR __init__.py:188-244)
+  * `GaussianRasterizer.markVisible(positions)` (DGR __init__.py:193-202)
+  * `rasterize_gaussians(...)` / `_RasterizeGaussians` (DGR __init__.py:21-171)
+
+Backward returns gradients for every Gaussian attribute plus the camera pose (`theta`, `rho`).  `means2D`,
+`theta` and `rho` are pure gradient sinks exactly as in the reference (never read by a kernel).
+
+Host code stays Python/PyTorch: it allocates tensors, selects device + current stream and calls the C ABI of
+`libsplat_raster.so` (include/splat_raster.h) through ctypes.  No CPU path exists.
+"""
+from __future__ import annotations
+
+from typing import NamedTuple
+
+import torch
+import torch.nn as nn
+
+from . import _cabi
+
+__all__ = ["GaussianRasterizationSettings", "GaussianRasterizer", "rasterize_gaussians"]
+
+
+def cpu_deep_copy_tuple(input_tuple):
+    copied_tensors = [item.cpu().clone() if isinstance(item, torch.Tensor) else item for item in input_tuple]
+    return tuple(copied_tensors)
+
+
+class GaussianRasterizationSettings(NamedTuple):
+    image_height: int
+    image_width: int
+    tanfovx: float
+    tanfovy: float
+    bg: torch.Tensor
+    scale_modifier: float
+    viewmatrix: torch.Tensor
+    projmatrix: torch.Tensor
+    projmatrix_raw: torch.Tensor
+    sh_degree: int
+    campos: torch.Tensor
+    prefiltered: bool
+    debug: bool
+
+
+def rasterize_gaussians(means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp, theta, rho,
+                        raster_settings):
+    return _RasterizeGaussians.apply(means3D, means2D, sh, colors_precomp, opacities, scales, rotations,
+                                     cov3Ds_precomp, theta, rho, raster_settings)
+
+
+class _PinnedInt:
+    """One pinned int32 per device for the num_rendered hand-off (the reference's blocking 4-byte cudaMemcpy,
+    DGR/cuda_rasterizer/rasterizer_impl.cu:284)."""
+    _slots = {}
+
+    @classmethod
+    def get(cls, device):
+        key = (device.type, device.index)
+        t = cls._slots.get(key)
+        if t is None:
+            t = torch.zeros(1, dtype=torch.int32).pin_memory()
+            cls._slots[key] = t
+        return t
+
+
+def _forward_impl(S, means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp):
+    """Equivalent of `_C.rasterize_gaussians` (DGR/rasterize_points.cu:35-122): returns
+    (num_rendered, color, radii, geomBuffer, binningBuffer, imgBuffer, depth, opacity, n_touched)."""
+    if means3D.ndimension() != 2 or means3D.size(1) != 3:
+        raise RuntimeError("means3D must have dimensions (num_points, 3)")
+    L = _cabi.lib()
+    means3D = _cabi.require_cuda("means3D", means3D)
+    dev = means3D.device
+    P, H, W = means3D.size(0), int(S.image_height), int(S.image_width)
+    f32 = dict(dtype=torch.float32, device=dev)
+    i32 = dict(dtype=torch.int32, device=dev)
+    with torch.cuda.device(dev):
+        stream = _cabi.stream_ptr(dev)
+        out_color = torch.empty((3, H, W), **f32)
+        out_depth = torch.empty((1, H, W), **f32)
+        out_opacity = torch.empty((1, H, W), **f32)
+        radii = torch.empty((P,), **i32)
+        n_touched = torch.empty((P,), **i32)
+        geom = torch.empty((L.splat_raster_geom_bytes(P),), dtype=torch.uint8, device=dev)
+        image = torch.empty((L.splat_raster_image_bytes(W, H),), dtype=torch.uint8, device=dev)
+        bg = _cabi.require_cuda("bg", S.bg)
+        M = 0
+        if sh.numel() != 0:
+            sh = _cabi.require_cuda("sh", sh)
+            M = sh.size(1)
+        if colors_precomp.numel() != 0:
+            colors_precomp = _cabi.require_cuda("colors_precomp", colors_precomp)
+        if scales.numel() != 0:
+            scales = _cabi.require_cuda("scales", scales)
+        if rotations.numel() != 0:
+            rotations = _cabi.require_cuda("rotations", rotations)
+        if cov3Ds_precomp.numel() != 0:
+            cov3Ds_precomp = _cabi.require_cuda("cov3Ds_precomp", cov3Ds_precomp)
+        opacities = _cabi.require_cuda("opacities", opacities) if P else opacities
+        view = _cabi.require_cuda("viewmatrix", S.viewmatrix)
+        proj = _cabi.require_cuda("projmatrix", S.projmatrix)
+        campos = _cabi.require_cuda("campos", S.campos)
+        host_R = _PinnedInt.get(dev)
+        rendered = 0
+        if P != 0:
+            _cabi.check(L.splat_raster_forward_preprocess(
+                P, int(S.sh_degree), M, W, H, _cabi.ptr(means3D), _cabi.ptr(scales), float(S.scale_modifier),
+                _cabi.ptr(rotations), _cabi.ptr(opacities), _cabi.ptr(sh), _cabi.ptr(cov3Ds_precomp),
+                _cabi.ptr(colors_precomp), _cabi.ptr(view), _cabi.ptr(proj), _cabi.ptr(campos), float(S.tanfovx),
+                float(S.tanfovy), int(bool(S.prefiltered)), radii.data_ptr(), n_touched.data_ptr(), geom.data_ptr(),
+                host_R.data_ptr(), stream), "forward_preprocess")
+            torch.cuda.current_stream(dev).synchronize()
+            rendered = int(host_R.item())
+        binning = torch.empty((L.splat_raster_binning_bytes(rendered),), dtype=torch.uint8, device=dev)
+        _cabi.check(L.splat_raster_forward_render(
+            P, rendered, W, H, _cabi.ptr(bg), _cabi.ptr(colors_precomp), _cabi.ptr(radii), geom.data_ptr(),
+            binning.data_ptr(), image.data_ptr(), out_color.data_ptr(), out_depth.data_ptr(), out_opacity.data_ptr(),
+            _cabi.ptr(n_touched), stream), "forward_render")
+        if S.debug:
+            torch.cuda.synchronize(dev)
+    return rendered, out_color, radii, geom, binning, image, out_depth, out_opacity, n_touched
+
+
+def _backward_impl(S, means3D, radii, colors_precomp, scales, rotations, cov3Ds_precomp, grad_out_color, grad_out_depth,
+                   sh, geom, num_rendered, binning, image):
+    """Equivalent of `_C.rasterize_gaussians_backward` (DGR/rasterize_points.cu:124-211) followed by the pose
+    reduction of DGR __init__.py:152-154. Returns (dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D,
+    dL_dsh, dL_dscales, dL_drotations, grad_tau[6])."""
+    L = _cabi.lib()
+    dev = means3D.device
+    P = means3D.size(0)
+    H, W = int(S.image_height), int(S.image_width)
+    M = sh.size(1) if sh.numel() != 0 else 0
+    f32 = dict(dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev):
+        stream = _cabi.stream_ptr(dev)
+        dL_dmeans3D = torch.empty((P, 3), **f32)
+        dL_dmeans2D = torch.empty((P, 3), **f32)
+        dL_dcolors = torch.empty((P, 3), **f32)
+        dL_dopacity = torch.empty((P, 1), **f32)
+        dL_dcov3D = torch.empty((P, 6), **f32)
+        dL_dsh = torch.empty((P, M, 3), **f32)
+        has_scale = scales.numel() != 0
+        dL_dscales = torch.empty((P, 3), **f32) if has_scale else torch.zeros((P, 3), **f32)
+        dL_drotations = torch.empty((P, 4), **f32) if has_scale else torch.zeros((P, 4), **f32)
+        nblk = (P + 255) // 256
+        tau_partial = torch.empty((nblk, 6), **f32)
+        scratch = torch.empty((P * 12,), **f32)
+        if P != 0:
+            gc = _cabi.require_cuda("grad_out_color", grad_out_color)
+            gd = _cabi.require_cuda("grad_out_depth", grad_out_depth)
+            _cabi.check(L.splat_raster_backward(
+                P, int(S.sh_degree), M, int(num_rendered), W, H, _cabi.ptr(_cabi.require_cuda("bg", S.bg)),
+                _cabi.ptr(means3D), _cabi.ptr(sh), _cabi.ptr(colors_precomp), _cabi.ptr(scales),
+                float(S.scale_modifier), _cabi.ptr(rotations), _cabi.ptr(cov3Ds_precomp),
+                _cabi.ptr(_cabi.require_cuda("viewmatrix", S.viewmatrix)),
+                _cabi.ptr(_cabi.require_cuda("projmatrix", S.projmatrix)),
+                _cabi.ptr(_cabi.require_cuda("projmatrix_raw", S.projmatrix_raw)),
+                _cabi.ptr(_cabi.require_cuda("campos", S.campos)), float(S.tanfovx), float(S.tanfovy),
+                radii.data_ptr(), geom.data_ptr(), binning.data_ptr(), image.data_ptr(), gc.data_ptr(), gd.data_ptr(),
+                scratch.data_ptr(), dL_dmeans2D.data_ptr(), dL_dcolors.data_ptr(), dL_dopacity.data_ptr(),
+                dL_dmeans3D.data_ptr(), dL_dcov3D.data_ptr(), _cabi.ptr(dL_dsh), dL_dscales.data_ptr(),
+                dL_drotations.data_ptr(), tau_partial.data_ptr(), stream), "backward")
+            grad_tau = tau_partial.sum(dim=0)
+        else:
+            grad_tau = torch.zeros(6, **f32)
+        if S.debug:
+            torch.cuda.synchronize(dev)
+    return dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations, grad_tau
+
+
+class _RasterizeGaussians(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp, theta, rho,
+                raster_settings):
+        args = (raster_settings, means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp)
+        if raster_settings.debug:
+            cpu_args = cpu_deep_copy_tuple(args[1:])  # copy them before they can be corrupted
+            try:
+                res = _forward_impl(*args)
+            except Exception as ex:
+                torch.save(cpu_args, "snapshot_fw.dump")
+                print("\nAn error occured in forward. Please forward snapshot_fw.dump for debugging.")
+                raise ex
+        else:
+            res = _forward_impl(*args)
+        num_rendered, color, radii, geomBuffer, binningBuffer, imgBuffer, depth, opacity, n_touched = res
+
+        ctx.raster_settings = raster_settings
+        ctx.num_rendered = num_rendered
+        ctx.save_for_backward(colors_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh, geomBuffer,
+                              binningBuffer, imgBuffer)
+        ctx.mark_non_differentiable(radii, n_touched)
+        return color, radii, depth, opacity, n_touched
+
+    @staticmethod
+    def backward(ctx, grad_out_color, grad_out_radii, grad_out_depth, grad_out_opacity, grad_n_touched):
+        # grad_out_opacity / radii / n_touched are ignored, as in the reference (DGR __init__.py:116-138)
+        S = ctx.raster_settings
+        colors_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh, geomBuffer, binningBuffer, imgBuffer = \
+            ctx.saved_tensors
+        dev = means3D.device
+        H, W = int(S.image_height), int(S.image_width)
+        if grad_out_color is None:
+            grad_out_color = torch.zeros((3, H, W), dtype=torch.float32, device=dev)
+        if grad_out_depth is None:
+            grad_out_depth = torch.zeros((1, H, W), dtype=torch.float32, device=dev)
+        args = (S, _cabi.require_cuda("means3D", means3D), radii, colors_precomp, scales, rotations, cov3Ds_precomp,
+                grad_out_color, grad_out_depth, sh, geomBuffer, ctx.num_rendered, binningBuffer, imgBuffer)
+        if S.debug:
+            cpu_args = cpu_deep_copy_tuple(args[1:])
+            try:
+                res = _backward_impl(*args)
+            except Exception as ex:
+                torch.save(cpu_args, "snapshot_bw.dump")
+                print("\nAn error occured in backward. Writing snapshot_bw.dump for debugging.\n")
+                raise ex
+        else:
+            res = _backward_impl(*args)
+        (grad_means2D, grad_colors_precomp, grad_opacities, grad_means3D, grad_cov3Ds_precomp, grad_sh, grad_scales,
+         grad_rotations, grad_tau) = res
+        grad_rho = grad_tau[:3].view(1, -1)
+        grad_theta = grad_tau[3:].view(1, -1)
+        grads = (grad_means3D, grad_means2D, grad_sh, grad_colors_precomp, grad_opacities, grad_scales, grad_rotations,
+                 grad_cov3Ds_precomp, grad_theta, grad_rho, None)
+        return grads
+
+
+class GaussianRasterizer(nn.Module):
+    def __init__(self, raster_settings):
+        super().__init__()
+        self.raster_settings = raster_settings
+
+    def markVisible(self, positions):
+        """Boolean mask of points in front of the near plane (DGR __init__.py:193-202)."""
+        with torch.no_grad():
+            S = self.raster_settings
+            positions = _cabi.require_cuda("positions", positions)
+            P = positions.size(0)
+            present = torch.zeros((P,), dtype=torch.bool, device=positions.device)
+            if P != 0:
+                with torch.cuda.device(positions.device):
+                    _cabi.check(_cabi.lib().splat_raster_mark_visible(
+                        P, positions.data_ptr(), _cabi.ptr(_cabi.require_cuda("viewmatrix", S.viewmatrix)),
+                        _cabi.ptr(_cabi.require_cuda("projmatrix", S.projmatrix)), present.data_ptr(),
+                        _cabi.stream_ptr(positions.device)), "mark_visible")
+        return present
+
+    def forward(self, means3D, means2D, opacities, shs=None, colors_precomp=None, scales=None, rotations=None,
+                cov3D_precomp=None, theta=None, rho=None):
+        raster_settings = self.raster_settings
+
+        if (shs is None and colors_precomp is None) or (shs is not None and colors_precomp is not None):
+            raise Exception('Please provide excatly one of either SHs or precomputed colors!')
+
+        if ((scales is None or rotations is None) and cov3D_precomp is None) or \
+                ((scales is not None or rotations is not None) and cov3D_precomp is not None):
+            raise Exception('Please provide exactly one of either scale/rotation pair or precomputed 3D covariance!')
+
+        if shs is None:
+            shs = torch.Tensor([])
+        if colors_precomp is None:
+            colors_precomp = torch.Tensor([])
+        if scales is None:
+            scales = torch.Tensor([])
+        if rotations is None:
+            rotations = torch.Tensor([])
+        if cov3D_precomp is None:
+            cov3D_precomp = torch.Tensor([])
+        if theta is None:
+            theta = torch.Tensor([])
+        if rho is None:
+            rho = torch.Tensor([])
+
+        return rasterize_gaussians(means3D, means2D, shs, colors_precomp, opacities, scales, rotations, cov3D_precomp,
+                                   theta, rho, raster_settings)
