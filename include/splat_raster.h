@@ -110,6 +110,21 @@ typedef struct splat_raster_views {
 int splat_raster_debug_views(int P, int R, int W, int H, void* geom, void* binning, void* image,
                              splat_raster_views* out);
 
+/* ---- diagnostics (measurement aids for bench.py; no counterpart in the reference, whose only aid is
+ * debug=true -> cudaDeviceSynchronize after each stage, DGR/cuda_rasterizer/auxiliary.h:166-173) ---- */
+
+/* Number of kernels this library has launched in this process (optionally reset). */
+unsigned long long splat_raster_launch_count(int reset);
+
+/* Per-stage timing with CUDA events recorded on the launching stream. Off by default; when on, each stage is
+ * bracketed by two event records and harvested lazily. Returns the previous setting. */
+int splat_raster_profile(int enable);
+int splat_raster_stage_count(void);
+const char* splat_raster_stage_name(int stage);
+/* ms_out[stage] = accumulated milliseconds, calls_out[stage] = number of timed executions (arrays of
+ * splat_raster_stage_count() entries). Synchronises on outstanding events. */
+int splat_raster_profile_read(float* ms_out, int* calls_out, int reset);
+
 #ifdef __cplusplus
 }
 #endif

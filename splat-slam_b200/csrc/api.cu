@@ -7,6 +7,51 @@ using namespace splat;
 
 namespace {
 inline int grid_dim(int v) { return (v + SPLAT_TILE - 1) / SPLAT_TILE; }
+
+// ---- diagnostics: kernel-launch counter and optional per-stage CUDA-event timing ------------------------
+enum Stage { ST_PREPROCESS = 0, ST_SCAN, ST_DUP, ST_SORT, ST_RECORDS, ST_RENDER_FWD, ST_ZERO, ST_RENDER_BWD,
+             ST_PREPROCESS_BWD, ST_COUNT };
+const char* kStageNames[ST_COUNT] = {"preprocess_forward", "scan_block_sums", "duplicate_with_keys", "radix_sort",
+                                     "ranges_and_records", "render_forward", "zero_grad_scratch", "render_backward",
+                                     "preprocess_backward"};
+unsigned long long g_launches = 0;
+int g_prof = 0;
+int g_prof_dev = -1;
+cudaEvent_t g_ev[ST_COUNT][2];
+bool g_pending[ST_COUNT];
+float g_ms[ST_COUNT];
+int g_calls[ST_COUNT];
+
+void prof_harvest(int st) {
+    if (!g_pending[st]) return;
+    float ms = 0.0f;
+    if (cudaEventSynchronize(g_ev[st][1]) == cudaSuccess && cudaEventElapsedTime(&ms, g_ev[st][0], g_ev[st][1]) == cudaSuccess) {
+        g_ms[st] += ms;
+        g_calls[st] += 1;
+    }
+    g_pending[st] = false;
+}
+void prof_begin(int st, cudaStream_t s) {
+    if (!g_prof) return;
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (g_prof_dev != dev) {   // events belong to a device: (re)create them for the current one
+        for (int i = 0; i < ST_COUNT; ++i) {
+            cudaEventCreate(&g_ev[i][0]);
+            cudaEventCreate(&g_ev[i][1]);
+            g_pending[i] = false;
+        }
+        g_prof_dev = dev;
+    }
+    prof_harvest(st);
+    cudaEventRecord(g_ev[st][0], s);
+}
+void prof_end(int st, cudaStream_t s, int kernels) {
+    g_launches += (unsigned long long)kernels;
+    if (!g_prof) return;
+    cudaEventRecord(g_ev[st][1], s);
+    g_pending[st] = true;
+}
 }  // namespace
 
 extern "C" {
@@ -65,9 +110,13 @@ int splat_raster_forward_preprocess(int P, int D, int M, int W, int H, const flo
     p.cov3D_precomp = cov3D_precomp; p.colors_precomp = colors_precomp;
     p.viewmatrix = viewmatrix; p.projmatrix = projmatrix; p.campos = campos;
     p.radii = radii; p.n_touched = n_touched;
+    prof_begin(ST_PREPROCESS, s);
     launch_preprocess_forward(p, g, s);
+    prof_end(ST_PREPROCESS, s, 1);
     SPLAT_CUDA_CHECK_LAUNCH();
+    prof_begin(ST_SCAN, s);
     launch_scan_block_sums(P, g, s);
+    prof_end(ST_SCAN, s, 1);
     SPLAT_CUDA_CHECK_LAUNCH();
     if (num_rendered_host) {
         cudaError_t e = cudaMemcpyAsync(num_rendered_host, g.num_rendered, sizeof(int), cudaMemcpyDeviceToHost, s);
@@ -92,15 +141,23 @@ int splat_raster_forward_render(int P, int R, int W, int H, const float* backgro
         // unsorted keys go where an odd/even number of ping-pong passes ends in b.keys / b.point_list
         uint64_t* k0 = (passes & 1) ? b.keys_alt : b.keys;
         uint32_t* v0 = (passes & 1) ? b.vals_alt : b.point_list;
+        prof_begin(ST_DUP, s);
         launch_duplicate_with_keys(P, gx, gy, radii, g, k0, v0, s);
+        prof_end(ST_DUP, s, 1);
         SPLAT_CUDA_CHECK_LAUNCH();
+        prof_begin(ST_SORT, s);
         launch_radix_sort(R, passes, b, s);
+        prof_end(ST_SORT, s, 3 * passes);
         SPLAT_CUDA_CHECK_LAUNCH();
     }
+    prof_begin(ST_RECORDS, s);
     launch_ranges_and_records(R, gx * gy, colors_precomp, g, b, im.ranges, s);
+    prof_end(ST_RECORDS, s, R > 0 ? 1 : 0);
     SPLAT_CUDA_CHECK_LAUNCH();
+    prof_begin(ST_RENDER_FWD, s);
     launch_render_forward(W, H, gx, gy, im.ranges, b.records, background, im.final_T, im.n_contrib, out_color,
                           out_depth, out_opacity, n_touched, s);
+    prof_end(ST_RENDER_FWD, s, 1);
     SPLAT_CUDA_CHECK_LAUNCH();
     return SPLAT_OK;
 }
@@ -127,11 +184,15 @@ int splat_raster_backward(int P, int D, int M, int R, int W, int H, const float*
     GeomState g = GeomState::carve(geom, (size_t)P, nullptr);
     BinningState b = BinningState::carve(binning, (size_t)R, nullptr);
     ImageState im = ImageState::carve(image, (size_t)W * H, (size_t)gx * gy, nullptr);
+    prof_begin(ST_ZERO, s);
     cudaError_t e = cudaMemsetAsync(grad_scratch, 0, sizeof(float) * SPLAT_GRAD_FLOATS * (size_t)P, s);
+    prof_end(ST_ZERO, s, 0);
     if (e != cudaSuccess) return (int)e;
     if (R > 0) {
+        prof_begin(ST_RENDER_BWD, s);
         launch_render_backward(W, H, gx, gy, im.ranges, b.records, background, im.final_T, im.n_contrib, dL_dout_color,
                                dL_dout_depth, grad_scratch, s);
+        prof_end(ST_RENDER_BWD, s, 1);
         SPLAT_CUDA_CHECK_LAUNCH();
     }
     BwdParams p;
@@ -146,7 +207,9 @@ int splat_raster_backward(int P, int D, int M, int R, int W, int H, const float*
     p.dL_dmean2D = dL_dmeans2D; p.dL_dcolors = dL_dcolors; p.dL_dopacity = dL_dopacity; p.dL_dmean3D = dL_dmeans3D;
     p.dL_dcov3D = dL_dcov3D; p.dL_dsh = dL_dsh; p.dL_dscale = dL_dscales; p.dL_drot = dL_drotations;
     p.dL_dtau = dL_dtau_partial;
+    prof_begin(ST_PREPROCESS_BWD, s);
     launch_preprocess_backward(p, g, s);
+    prof_end(ST_PREPROCESS_BWD, s, 1);
     SPLAT_CUDA_CHECK_LAUNCH();
     return SPLAT_OK;
 }
@@ -158,6 +221,7 @@ int splat_raster_mark_visible(int P, const float* means3D, const float* viewmatr
     if (P == 0) return SPLAT_OK;
     if (!means3D || !viewmatrix || !present) return SPLAT_ERR_ARG;
     launch_mark_visible(P, means3D, viewmatrix, reinterpret_cast<bool*>(present), (cudaStream_t)stream);
+    g_launches += 1;
     SPLAT_CUDA_CHECK_LAUNCH();
     return SPLAT_OK;
 }
@@ -180,6 +244,33 @@ int splat_raster_debug_views(int P, int R, int W, int H, void* geom, void* binni
     out->ranges = reinterpret_cast<const unsigned int*>(im.ranges);
     out->final_T = im.final_T;
     out->n_contrib = im.n_contrib;
+    return SPLAT_OK;
+}
+
+unsigned long long splat_raster_launch_count(int reset) {
+    const unsigned long long v = g_launches;
+    if (reset) g_launches = 0;
+    return v;
+}
+
+int splat_raster_profile(int enable) {
+    const int old = g_prof;
+    g_prof = enable ? 1 : 0;
+    return old;
+}
+
+int splat_raster_stage_count(void) { return ST_COUNT; }
+
+const char* splat_raster_stage_name(int stage) { return (stage >= 0 && stage < ST_COUNT) ? kStageNames[stage] : ""; }
+
+int splat_raster_profile_read(float* ms_out, int* calls_out, int reset) {
+    if (!ms_out || !calls_out) return SPLAT_ERR_ARG;
+    for (int i = 0; i < ST_COUNT; ++i) {
+        if (g_prof_dev >= 0) prof_harvest(i);
+        ms_out[i] = g_ms[i];
+        calls_out[i] = g_calls[i];
+        if (reset) { g_ms[i] = 0.0f; g_calls[i] = 0; }
+    }
     return SPLAT_OK;
 }
 

@@ -31,7 +31,8 @@ class _Views(ctypes.Structure):
 EXPORTS = (
     "splat_raster_abi_version", "splat_raster_geom_bytes", "splat_raster_image_bytes", "splat_raster_binning_bytes",
     "splat_raster_forward_preprocess", "splat_raster_forward_render", "splat_raster_backward",
-    "splat_raster_mark_visible", "splat_raster_debug_views",
+    "splat_raster_mark_visible", "splat_raster_debug_views", "splat_raster_launch_count", "splat_raster_profile",
+    "splat_raster_stage_count", "splat_raster_stage_name", "splat_raster_profile_read",
 )
 
 
@@ -63,6 +64,15 @@ def lib() -> ctypes.CDLL:
     L.splat_raster_mark_visible.argtypes = [c_int, P, P, P, P, P]
     L.splat_raster_debug_views.restype = c_int
     L.splat_raster_debug_views.argtypes = [c_int] * 4 + [P, P, P, POINTER(_Views)]
+    L.splat_raster_launch_count.restype = ctypes.c_ulonglong
+    L.splat_raster_launch_count.argtypes = [c_int]
+    L.splat_raster_profile.restype = c_int
+    L.splat_raster_profile.argtypes = [c_int]
+    L.splat_raster_stage_count.restype = c_int
+    L.splat_raster_stage_name.restype = ctypes.c_char_p
+    L.splat_raster_stage_name.argtypes = [c_int]
+    L.splat_raster_profile_read.restype = c_int
+    L.splat_raster_profile_read.argtypes = [POINTER(c_float), POINTER(c_int), c_int]
     if L.splat_raster_abi_version() != ABI_VERSION:
         raise SplatRasterError("libsplat_raster.so ABI version mismatch; rebuild")
     _lib = L
@@ -125,3 +135,21 @@ def debug_views(P, R, W, H, geom, binning, image):
     )
     assert dev == out["depths"].device
     return out
+
+
+def launch_count(reset: bool = False) -> int:
+    return int(lib().splat_raster_launch_count(1 if reset else 0))
+
+
+def profile(enable: bool) -> bool:
+    return bool(lib().splat_raster_profile(1 if enable else 0))
+
+
+def profile_read(reset: bool = True):
+    """{stage name: (total ms, calls)} measured with CUDA events on the launching stream."""
+    L = lib()
+    n = L.splat_raster_stage_count()
+    ms = (c_float * n)()
+    calls = (c_int * n)()
+    check(L.splat_raster_profile_read(ms, calls, 1 if reset else 0), "profile_read")
+    return {L.splat_raster_stage_name(i).decode(): (float(ms[i]), int(calls[i])) for i in range(n)}

@@ -1,0 +1,223 @@
+"""GPU (B200): parity of the CUDA path, called through the public API -> ctypes -> C ABI.
+
+Three checkers, in order of strength:
+  1. the compiled reference extension itself (oracle/_ref/ref_dgr) on identical inputs in the same process:
+     sort keys, point list, radii, tile ranges, n_touched, n_contrib, final_T and the per-Gaussian geometry
+     BIT-EXACT; color/depth/opacity <= 1e-5 abs; gradients <= 1e-3 relative;
+  2. the committed golden vectors (outputs of that reference on a B200), same bars — works when ref_dgr is absent;
+  3. the CPU oracle (1e-5-class agreement up to borderline flips), plus size-independent properties at full size.
+"""
+import glob
+import os
+
+import pytest
+import torch
+
+import parity as T
+from test_oracle_golden import GOLDEN, case_from_fixture
+
+pytestmark = pytest.mark.gpu
+
+CASES = {
+    "tiny_sh0": dict(camera="tiny", P=300),
+    "single": dict(camera="tiny", P=1, seed=4, near_frac=0.0),
+    "ragged_sh1_bg": dict(camera="ragged", P=1500, sh_coeffs=4, sh_degree=1, bg=(0.2, 0.5, 0.7), view_k=2),
+    "ragged_sh2": dict(camera="ragged", P=900, sh_coeffs=9, sh_degree=2, view_k=4, seed=2),
+    "small_sh3": dict(camera="small", P=20000, sh_coeffs=16, sh_degree=3, view_k=1),
+    "small_M16_D0": dict(camera="small", P=3000, sh_coeffs=16, sh_degree=0, view_k=5),
+    "small_precomp": dict(camera="small", P=20000, use_colors_precomp=True, use_cov3d_precomp=True, view_k=3),
+    "small_colors_only": dict(camera="small", P=4000, use_colors_precomp=True, view_k=6),
+    "big_splats": dict(camera="small", P=5000, scale_modifier=1.7, sigma_px=6.0),
+    "huge_splats": dict(camera="ragged", P=64, sigma_px=200.0, seed=8),
+    "tum_200k": dict(camera="tum", P=200000, view_k=1),
+}
+
+
+def _make(kw):
+    kw = dict(kw)
+    near = kw.pop("near_frac", None)
+    case = T.make_case(**kw)
+    if near is not None:
+        from diff_gaussian_rasterization import synthetic as syn
+        g = syn.make_gaussians(kw["camera"], kw["P"], seed=kw.get("seed", 0), near_frac=near)
+        for k in ("means3D", "opacities", "scales", "rotations", "shs"):
+            case[k] = g[k]
+    return case
+
+
+needs_ref = pytest.mark.skipif(T.load_ref() is None, reason="oracle/_ref/ref_dgr not built")
+
+
+@needs_ref
+@pytest.mark.parametrize("name", list(CASES))
+def test_bit_exact_chain_vs_reference_extension(name):
+    case = _make(CASES[name])
+    ours = T.ours_forward_with_intermediates(case)
+    ref = T.ref_forward_with_intermediates(T.load_ref(), case)
+    T.compare_intermediates(ours, ref)
+    assert int((~T.bits_equal(ours["final_T"], ref["final_T"])).sum()) == 0
+    for k in ("color", "depth", "opacity"):
+        assert float((ours[k] - ref[k]).abs().max()) <= T.FWD_ATOL
+
+
+@needs_ref
+@pytest.mark.parametrize("name", list(CASES))
+def test_outputs_and_gradients_vs_reference_extension(name):
+    case = _make(CASES[name])
+    ours = T.run_module(T.load_ours(), case)
+    ref = T.run_module(T.load_ref(), case)
+    rep = T.compare_outputs(ours, ref, exact_ints=True)
+    assert rep
+
+
+@pytest.mark.parametrize("path", GOLDEN, ids=[os.path.basename(p)[:-3] for p in GOLDEN])
+def test_vs_golden_vectors(path):
+    fx = torch.load(path, weights_only=False)
+    case = case_from_fixture(fx)
+    inter = T.ours_forward_with_intermediates(case)
+    assert inter["num_rendered"] == fx["num_rendered"]
+    for k in ("radii", "n_touched", "keys", "point_list", "n_contrib", "tiles_touched"):
+        assert torch.equal(inter[k].cpu().long().reshape(-1), fx[k].long().reshape(-1)), k
+    assert torch.equal(inter["ranges"].cpu().long(), fx["ranges"].long())
+    vis = fx["radii"] > 0
+    for k in ("depths", "means2D", "conic_opacity"):
+        assert bool(T.bits_equal(inter[k].cpu()[vis], fx[k][vis]).all()), k
+    assert bool(T.bits_equal(inter["final_T"], fx["final_T"]).all())
+    ours = T.run_module(T.load_ours(), case)
+    T.compare_outputs(ours, fx, exact_ints=True)
+
+
+@pytest.mark.parametrize("name", ["tiny_sh0", "ragged_sh1_bg", "small_precomp", "big_splats"])
+def test_vs_cpu_oracle(name):
+    case = _make(CASES[name])
+    if case["P"] > 6000:       # keep the CPU side in seconds
+        case = _make(dict(CASES[name], P=5000))
+    ours = T.run_module(T.load_ours(), case)
+    orc = T.run_oracle(case)
+    T.compare_outputs(ours, orc, exact_ints=False, int_mismatch_frac=0.02, fwd_atol=5e-4, grad_rtol=5e-3)
+
+
+# ---- edge cases -------------------------------------------------------------------------------------------
+def test_zero_gaussians():
+    m = T.load_ours()
+    case = T.make_case(camera="tiny", P=4)
+    S = T.settings_for(m, dict(case, bg=torch.tensor([0.3, 0.6, 0.9])), "cuda")
+    z3 = torch.zeros(0, 3, device="cuda", requires_grad=True)
+    color, radii, depth, opacity, n_touched = m.GaussianRasterizer(S)(
+        means3D=z3, means2D=torch.zeros(0, 3, device="cuda"), opacities=torch.zeros(0, 1, device="cuda"),
+        shs=torch.zeros(0, 1, 3, device="cuda"), scales=torch.zeros(0, 3, device="cuda"),
+        rotations=torch.zeros(0, 4, device="cuda"))
+    assert radii.numel() == 0 and n_touched.numel() == 0
+    assert torch.allclose(color, torch.tensor([0.3, 0.6, 0.9], device="cuda")[:, None, None].expand_as(color))
+    assert float(depth.abs().max()) == 0 and float(opacity.abs().max()) == 0
+    color.sum().backward()
+    assert z3.grad.shape == (0, 3)
+
+
+def test_everything_culled():
+    """All Gaussians behind the near plane: num_rendered = 0, background image, zero gradients."""
+    m = T.load_ours()
+    case = T.make_case(camera="tiny", P=200, bg=(0.5, 0.25, 0.125))
+    case["means3D"] = case["means3D"].clone()
+    case["means3D"][:, 2] = -case["means3D"][:, 2].abs() - 0.01
+    out = T.run_module(m, case)
+    assert int(out["radii"].abs().sum()) == 0 and int(out["n_touched"].sum()) == 0
+    assert float((out["color"] - case["bg"].cuda()[:, None, None]).abs().max()) == 0
+    for k in ("means3D", "shs", "opacities", "scales", "rotations", "theta", "rho"):
+        assert float(out["grad_" + k].abs().max()) == 0, k
+
+
+def test_near_plane_is_0p001():
+    """As-installed near plane (Dockerfile:20): z = 0.0011 is kept, z = 0.001 is culled (p_view.z <= 0.001f)."""
+    m = T.load_ours()
+    case = T.make_case(camera="tiny", P=2)
+    S = T.settings_for(m, case, "cuda")
+    pts = torch.tensor([[0.0, 0.0, 0.0011], [0.0, 0.0, 0.001], [0.0, 0.0, 0.19], [0.0, 0.0, -1.0]], device="cuda")
+    vis = m.GaussianRasterizer(S).markVisible(pts)
+    assert vis.tolist() == [True, False, True, False]
+
+
+@needs_ref
+def test_mark_visible_vs_reference():
+    m, ref = T.load_ours(), T.load_ref()
+    case = T.make_case(camera="small", P=50000, view_k=2)
+    pts = case["means3D"].cuda()
+    a = m.GaussianRasterizer(T.settings_for(m, case, "cuda")).markVisible(pts)
+    b = ref.GaussianRasterizer(T.settings_for(ref, case, "cuda")).markVisible(pts)
+    assert torch.equal(a, b)
+
+
+def test_pose_only_gradients():
+    """BASELINE config 3 shape: only theta/rho require grad (MonoGS-style tracking)."""
+    m = T.load_ours()
+    case = T.make_case(camera="small", P=3000, view_k=1)
+    S = T.settings_for(m, case, "cuda")
+    theta = torch.zeros(3, device="cuda", requires_grad=True)
+    rho = torch.zeros(3, device="cuda", requires_grad=True)
+    color, radii, depth, opacity, n_touched = m.GaussianRasterizer(S)(
+        means3D=case["means3D"].cuda(), means2D=torch.zeros(3000, 3, device="cuda"), opacities=case["opacities"].cuda(),
+        shs=case["shs"].cuda(), scales=case["scales"].cuda(), rotations=case["rotations"].cuda(), theta=theta, rho=rho)
+    ((color * case["Wc"].cuda()).sum() + (depth * case["Wd"].cuda()).sum()).backward()
+    full = T.run_module(m, case)
+    assert T.rel_err(theta.grad, full["grad_theta"]) < 1e-4 and T.rel_err(rho.grad, full["grad_rho"]) < 1e-4
+    assert float(theta.grad.abs().max()) > 0
+
+
+def test_non_default_stream_and_repeatability():
+    m = T.load_ours()
+    case = T.make_case(camera="small", P=4000, view_k=2)
+    a = T.run_module(m, case, with_grad=False)
+    s = torch.cuda.Stream()
+    with torch.cuda.stream(s):
+        b = T.run_module(m, case, with_grad=False)
+    s.synchronize()
+    for k in ("color", "depth", "opacity", "radii", "n_touched"):
+        assert torch.equal(a[k], b[k]), k
+
+
+# ---- size-independent properties at full BASELINE size --------------------------------------------------
+def test_full_size_properties():
+    case = T.make_case(camera="replica", P=1_000_000)
+    o = T.ours_forward_with_intermediates(case)
+    R = o["num_rendered"]
+    keys = o["keys"]
+    assert R == int(o["tiles_touched"].long().sum())
+    assert bool((keys[1:] >= keys[:-1]).all()), "keys sorted"
+    tiles = (keys >> 32)
+    ranges = o["ranges"].long()
+    counts = torch.bincount(tiles, minlength=ranges.shape[0])
+    assert torch.equal(ranges[:, 1] - ranges[:, 0], counts), "ranges = per-tile histogram"
+    nz = counts > 0
+    assert torch.equal(ranges[nz, 0], (torch.cumsum(counts, 0) - counts)[nz])
+    # the sort is a permutation of the emitted instances: per-Gaussian multiplicity = tiles_touched
+    mult = torch.bincount(o["point_list"].long(), minlength=case["P"])
+    assert torch.equal(mult, o["tiles_touched"].long())
+    # depth bits in the key equal the Gaussian's stored depth
+    d = o["depths"][o["point_list"].long()].view(torch.int32).long() & 0xFFFFFFFF
+    assert torch.equal(keys & 0xFFFFFFFF, d)
+    # stability: equal keys keep ascending Gaussian id (emission order)
+    same = keys[1:] == keys[:-1]
+    assert bool((o["point_list"].long()[1:][same] > o["point_list"].long()[:-1][same]).all())
+    # compositing invariants
+    T_ = o["final_T"]
+    assert float(T_.min()) >= 0.0 and float(T_.max()) <= 1.0
+    assert torch.allclose(o["opacity"][0], 1.0 - T_, atol=1e-6)
+    lens = (ranges[:, 1] - ranges[:, 0])
+    H, W = T_.shape
+    ty = torch.arange(H, device="cuda") // 16
+    tx = torch.arange(W, device="cuda") // 16
+    tile_of_pix = ty[:, None] * ((W + 15) // 16) + tx[None, :]
+    assert bool((o["n_contrib"].long() <= lens[tile_of_pix]).all())
+    assert int(o["n_touched"].min()) >= 0 and int((o["n_touched"][o["radii"] == 0]).sum()) == 0
+    assert bool(torch.isfinite(o["color"]).all() and torch.isfinite(o["depth"]).all())
+
+
+def test_linearity_in_upstream_gradient():
+    """Backward is linear in (dL/dcolor, dL/ddepth): grads(2*Wc, 2*Wd) = 2*grads(Wc, Wd)."""
+    m = T.load_ours()
+    case = T.make_case(camera="small", P=5000, view_k=3)
+    a = T.run_module(m, case)
+    case2 = dict(case, Wc=2 * case["Wc"], Wd=2 * case["Wd"])
+    b = T.run_module(m, case2)
+    for k in ("means3D", "shs", "opacities", "scales", "rotations", "theta", "rho"):
+        assert T.rel_err(b["grad_" + k], 2 * a["grad_" + k]) < 1e-4, k
