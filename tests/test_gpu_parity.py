@@ -94,7 +94,7 @@ def test_vs_cpu_oracle(name):
         case = _make(dict(CASES[name], P=5000))
     ours = T.run_module(T.load_ours(), case)
     orc = T.run_oracle(case)
-    T.compare_outputs(ours, orc, exact_ints=False, int_mismatch_frac=0.02, fwd_atol=5e-4, grad_rtol=5e-3)
+    T.compare_vs_cpu_oracle(ours, orc)
 
 
 # ---- edge cases -------------------------------------------------------------------------------------------
