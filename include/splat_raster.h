@@ -87,6 +87,40 @@ int splat_raster_backward(
     float* dL_dmeans2D, float* dL_dcolors, float* dL_dopacity, float* dL_dmeans3D, float* dL_dcov3D,
     float* dL_dsh, float* dL_dscales, float* dL_drotations, float* dL_dtau_partial, void* stream);
 
+/* Backward for hosts that have no way to obtain device memory at call time. (No counterpart in the reference: its
+ * backward allocates eleven tensors per call through torch, DGR/rasterize_points.cu:160-170.)
+ *
+ * splat_raster_backward needs `grad_scratch`, P*12 floats that somebody has to allocate. Some users of this library
+ * cannot do that where the call happens: a pose-tracking loop that must keep a fixed frame time (cudaFree waits for
+ * the whole device to go idle and cudaMalloc may, which also holds up the mapper process sharing the GPU), a
+ * host that handed all of its device memory to fixed pools at start-up, or a thin binding in a language runtime
+ * that only forwards the tensors it was given. For them this entry point keeps the scratch inside the library, in a
+ * fixed device array of SPLAT_NOALLOC_MAX_GAUSSIANS * 12 floats (12 MiB per GPU, held from the moment the library
+ * is loaded on that GPU until the process ends). It calls no cudaMalloc/cudaFree and no allocating library routine;
+ * the caller still passes every input and output, exactly as for splat_raster_backward minus `grad_scratch`.
+ *
+ *   - P above SPLAT_NOALLOC_MAX_GAUSSIANS is refused with SPLAT_ERR_CAPACITY before anything is launched; use
+ *     splat_raster_backward with your own scratch for larger clouds.
+ *   - The first call on each device looks up where the array lives on that device (cudaGetSymbolAddress, with that
+ *     device current) and remembers it. Make that first call before starting any stream capture.
+ *   - All calls on one GPU share the one array. It still holds the sums of the previous call, so each call first
+ *     clears the P*12 floats it is about to accumulate into. Two calls whose GPU work overlaps (different streams,
+ *     or different host threads) would clear and add to the same floats at the same time and corrupt each other:
+ *     keep calls on one device ordered on one stream, or serialise them yourself.
+ * Results equal those of splat_raster_backward up to the summation order of float atomics. */
+#define SPLAT_NOALLOC_MAX_GAUSSIANS 262144
+#define SPLAT_ERR_CAPACITY (-3) /* more Gaussians than the built-in scratch of the *_noalloc entry point can hold */
+int splat_raster_backward_noalloc(
+    int P, int D, int M, int R, int W, int H,
+    const float* background, const float* means3D, const float* shs, const float* colors_precomp,
+    const float* scales, float scale_modifier, const float* rotations, const float* cov3D_precomp,
+    const float* viewmatrix, const float* projmatrix, const float* projmatrix_raw, const float* campos,
+    float tan_fovx, float tan_fovy, const int* radii,
+    void* geom, void* binning, void* image,
+    const float* dL_dout_color, const float* dL_dout_depth,
+    float* dL_dmeans2D, float* dL_dcolors, float* dL_dopacity, float* dL_dmeans3D, float* dL_dcov3D,
+    float* dL_dsh, float* dL_dscales, float* dL_drotations, float* dL_dtau_partial, void* stream);
+
 /* present[i] = Gaussian i passes the near-plane test. Replaces Rasterizer::markVisible / checkFrustum
  * (DGR/cuda_rasterizer/rasterizer_impl.cu:54-66,141-153). `present` is P bytes (bool). */
 int splat_raster_mark_visible(int P, const float* means3D, const float* viewmatrix, const float* projmatrix,

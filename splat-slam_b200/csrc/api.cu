@@ -247,6 +247,89 @@ int splat_raster_debug_views(int P, int R, int W, int H, void* geom, void* binni
     return SPLAT_OK;
 }
 
+}  // extern "C"
+
+// ---- backward without any allocation ---------------------------------------------------------------------
+// Scratch for splat_raster_backward_noalloc: the packed per-Gaussian render gradients (12 floats each) that the
+// regular entry point receives from its caller. 262144 Gaussians x 48 B = 12 MiB, resident on every GPU that loads
+// this library until the process exits. Device code may name the array directly; HOST code must not use the name as
+// an address (it is only a host-side handle for the symbol) and goes through cudaGetSymbolAddress below.
+static __device__ __align__(256) float g_noalloc_grad_scratch[(size_t)SPLAT_NOALLOC_MAX_GAUSSIANS * SPLAT_GRAD_FLOATS];
+
+namespace {
+constexpr int kNoAllocMaxDevices = 64;
+float* g_noalloc_ptr[kNoAllocMaxDevices];   // per device: where that device's copy of the array lives
+}  // namespace
+
+extern "C" {
+
+int splat_raster_backward_noalloc(int P, int D, int M, int R, int W, int H, const float* background,
+                                  const float* means3D, const float* shs, const float* colors_precomp,
+                                  const float* scales, float scale_modifier, const float* rotations,
+                                  const float* cov3D_precomp, const float* viewmatrix, const float* projmatrix,
+                                  const float* projmatrix_raw, const float* campos, float tan_fovx, float tan_fovy,
+                                  const int* radii, void* geom, void* binning, void* image,
+                                  const float* dL_dout_color, const float* dL_dout_depth, float* dL_dmeans2D,
+                                  float* dL_dcolors, float* dL_dopacity, float* dL_dmeans3D, float* dL_dcov3D,
+                                  float* dL_dsh, float* dL_dscales, float* dL_drotations, float* dL_dtau_partial,
+                                  void* stream) {
+    if (P < 0 || R < 0 || W <= 0 || H <= 0 || D < 0 || D > 3) return SPLAT_ERR_SIZE;
+    if (P > SPLAT_NOALLOC_MAX_GAUSSIANS) return SPLAT_ERR_CAPACITY;   // would not fit the built-in scratch
+    if (P == 0) return SPLAT_OK;
+    if (!geom || !binning || !image || !background || !means3D || !radii || !viewmatrix || !projmatrix ||
+        !projmatrix_raw || !dL_dout_color || !dL_dout_depth || !dL_dmeans2D || !dL_dcolors || !dL_dopacity ||
+        !dL_dmeans3D || !dL_dcov3D || !dL_dtau_partial)
+        return SPLAT_ERR_ARG;
+    if (shs && (!dL_dsh || !campos)) return SPLAT_ERR_ARG;
+    if (scales && (!rotations || !dL_dscales || !dL_drotations)) return SPLAT_ERR_ARG;
+
+    // One-time set-up per device, done by the first call made with that device current: ask the runtime where this
+    // device's copy of the array is. (Keep that first call outside of any stream capture.)
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return (int)e;
+    if (dev < 0 || dev >= kNoAllocMaxDevices) return SPLAT_ERR_ARG;
+    if (g_noalloc_ptr[dev] == nullptr) {
+        void* addr = nullptr;
+        e = cudaGetSymbolAddress(&addr, g_noalloc_grad_scratch);
+        if (e != cudaSuccess) return (int)e;
+        if (addr == nullptr) return SPLAT_ERR_ARG;
+        g_noalloc_ptr[dev] = static_cast<float*>(addr);
+    }
+    float* scratch = g_noalloc_ptr[dev];
+
+    cudaStream_t s = (cudaStream_t)stream;
+    const int gx = grid_dim(W), gy = grid_dim(H);
+    GeomState g = GeomState::carve(geom, (size_t)P, nullptr);
+    BinningState b = BinningState::carve(binning, (size_t)R, nullptr);
+    ImageState im = ImageState::carve(image, (size_t)W * H, (size_t)gx * gy, nullptr);
+    // the array still holds the previous call's sums: the part this call accumulates into starts from zero
+    e = cudaMemsetAsync(scratch, 0, sizeof(float) * SPLAT_GRAD_FLOATS * (size_t)P, s);
+    if (e != cudaSuccess) return (int)e;
+    if (R > 0) {
+        launch_render_backward(W, H, gx, gy, im.ranges, b.records, background, im.final_T, im.n_contrib, dL_dout_color,
+                               dL_dout_depth, scratch, s);
+        g_launches += 1;
+        SPLAT_CUDA_CHECK_LAUNCH();
+    }
+    BwdParams p;
+    p.P = P; p.D = D; p.M = M; p.R = R; p.W = W; p.H = H; p.grid_x = gx; p.grid_y = gy;
+    p.scale_modifier = scale_modifier; p.tanfovx = tan_fovx; p.tanfovy = tan_fovy;
+    p.focal_y = H / (2.0f * tan_fovy);
+    p.focal_x = W / (2.0f * tan_fovx);
+    p.bg = background; p.means3D = means3D; p.shs = shs; p.colors_precomp = colors_precomp; p.scales = scales;
+    p.rotations = rotations; p.cov3D_precomp = cov3D_precomp; p.viewmatrix = viewmatrix; p.projmatrix = projmatrix;
+    p.projmatrix_raw = projmatrix_raw; p.campos = campos; p.radii = radii;
+    p.dL_dpix = dL_dout_color; p.dL_dpix_depth = dL_dout_depth; p.grad_accum = scratch;
+    p.dL_dmean2D = dL_dmeans2D; p.dL_dcolors = dL_dcolors; p.dL_dopacity = dL_dopacity; p.dL_dmean3D = dL_dmeans3D;
+    p.dL_dcov3D = dL_dcov3D; p.dL_dsh = dL_dsh; p.dL_dscale = dL_dscales; p.dL_drot = dL_drotations;
+    p.dL_dtau = dL_dtau_partial;
+    launch_preprocess_backward(p, g, s);
+    g_launches += 1;
+    SPLAT_CUDA_CHECK_LAUNCH();
+    return SPLAT_OK;
+}
+
 unsigned long long splat_raster_launch_count(int reset) {
     const unsigned long long v = g_launches;
     if (reset) g_launches = 0;
