@@ -2,6 +2,7 @@
 // gather of per-instance render records.
 // Replaces cub::DeviceScan::InclusiveSum (DGR/cuda_rasterizer/rasterizer_impl.cu:280), duplicateWithKeys (:70-111),
 // getHigherMsb + cub::DeviceRadixSort::SortPairs (:35-50,303-311), cudaMemset + identifyTileRanges (:313-321,116-138).
+#include <cuda_fp16.h>
 #include "common.cuh"
 #include "kernels.h"
 
@@ -276,6 +277,31 @@ void launch_radix_sort(int R, int passes, const BinningState& b, cudaStream_t s)
 // One thread per sorted instance: detects tile boundaries (identifyTileRanges) and gathers the instance's
 // Gaussian into a 48-byte record {x, y, conic.x, conic.y | conic.z, opacity, depth, id | r, g, b, -} so the
 // render kernels stream contiguous records with bulk async copies instead of four dependent gathers.
+// Conservative axis-aligned half extents (hx, hy), packed as two round-up fp16, of the region where this instance
+// can pass the render kernels' alpha >= 1/255 test: alpha = o*exp(-q(d)) >= 1/255 needs q(d) <= tau = ln(255*o), and
+// {q <= tau} with q(d) = 0.5*(A dx^2 + C dy^2) + B dx dy is an ellipse whose bounding box has half widths
+// sqrt(2 tau C/det), sqrt(2 tau A/det). Margins (+0.01 on tau, x1.001, +0.05 px, fp16 round-up) cover float rounding
+// in power/expf, so a pixel the reference would blend is never outside the box. Degenerate conics -> "everywhere".
+__device__ __forceinline__ uint32_t footprint_half_extents(float4 co) {
+    const float A = co.x, B = co.y, C = co.z, o = co.w;
+    float hx = 65504.0f, hy = 65504.0f;
+    const float tau0 = logf(255.0f * o) + 0.02f;
+    const float det = A * C - B * B;
+    if (tau0 < 0.0f) {
+        hx = hy = -65504.0f;                      // opacity below 1/255: can never contribute
+    } else if (det > 0.0f && A > 0.0f && C > 0.0f) {
+        // the terms of `power` reach 2*tau*A*C/det near the ellipse, so its float rounding error scales with the
+        // anisotropy A*C/det: widen tau accordingly (negligible for ordinary splats, safe for needle-like ones)
+        const float tau = tau0 * (1.0f + 4e-6f * (A * C / det));
+        const float ex = sqrtf(2.0f * tau * C / det) * 1.001f + 0.05f;
+        const float ey = sqrtf(2.0f * tau * A / det) * 1.001f + 0.05f;
+        if (ex < 65504.0f) hx = ex;
+        if (ey < 65504.0f) hy = ey;
+    }
+    const __half2 h = __halves2half2(__float2half_ru(hx), __float2half_ru(hy));
+    return *reinterpret_cast<const uint32_t*>(&h);
+}
+
 __global__ void __launch_bounds__(256)
 ranges_and_records_kernel(int R, const uint64_t* __restrict__ keys, const uint32_t* __restrict__ point_list,
                           const float* __restrict__ colors, GeomState g, uint2* __restrict__ ranges,
@@ -297,7 +323,7 @@ ranges_and_records_kernel(int R, const uint64_t* __restrict__ keys, const uint32
     const float r = colors[3 * id], gg = colors[3 * id + 1], b = colors[3 * id + 2];
     records[3 * (size_t)i + 0] = make_float4(xy.x, xy.y, co.x, co.y);
     records[3 * (size_t)i + 1] = make_float4(co.z, co.w, d, __uint_as_float(id));
-    records[3 * (size_t)i + 2] = make_float4(r, gg, b, 0.0f);
+    records[3 * (size_t)i + 2] = make_float4(r, gg, b, __uint_as_float(footprint_half_extents(co)));
 }
 
 void launch_ranges_and_records(int R, int tiles, const float* colors_precomp, const GeomState& g,

@@ -7,6 +7,7 @@
 // cp.async.bulk (TMA 1-D bulk copy, SASS UBLKCP) completing on an mbarrier; the consumer loop reads them with
 // broadcast LDS.128. The backward reduces the 10 per-Gaussian gradient terms across the warp with a
 // recursive-halving shuffle tree (12 SHFL instead of 50) and issues one RED per term per warp.
+#include <cuda_fp16.h>
 #include "common.cuh"
 #include "kernels.h"
 
@@ -50,6 +51,41 @@ __device__ __forceinline__ void pixel_of_thread(int tile_x, int tile_y, uint32_t
     py = tile_y * SPLAT_TILE + (warp >> 1) * 4 + (lane >> 3);
 }
 
+// pixel rectangle [x0, x1] x [y0, y1] (inclusive, as floats) of this warp's 8x4 patch
+__device__ __forceinline__ float4 patch_of_warp(int tile_x, int tile_y) {
+    const uint32_t warp = threadIdx.x >> 5;
+    const float x0 = (float)(tile_x * SPLAT_TILE + (warp & 1) * 8), y0 = (float)(tile_y * SPLAT_TILE + (warp >> 1) * 4);
+    return make_float4(x0, y0, x0 + 7.0f, y0 + 3.0f);
+}
+
+// Per-warp binning of one staged batch: each lane tests cnt/32 records against the warp's pixel patch using the
+// conservative footprint box stored in the record (ranges_and_records_kernel) and the survivors' batch indices are
+// compacted, in order, into `list`. A (warp, instance) pair that cannot reach alpha >= 1/255 anywhere in the patch
+// then costs ~0.5 instructions instead of a full power/exp evaluation by all 32 lanes. Comparisons are written so
+// that NaN coordinates count as "inside" (the reference would still evaluate them). Returns the survivor count.
+__device__ __forceinline__ int bin_batch_for_warp(const float4* rec, int cnt, float4 patch, uint8_t* list,
+                                                  uint32_t lane) {
+    int n = 0;
+    const uint32_t lt = (1u << lane) - 1u;
+#pragma unroll
+    for (int r = 0; r < kBatch / 32; ++r) {
+        const int j = r * 32 + (int)lane;
+        bool live = false;
+        if (j < cnt) {
+            const float4 r0 = rec[3 * j];
+            const uint32_t hw = __float_as_uint(rec[3 * j + 2].w);
+            const float2 h = __half22float2(*reinterpret_cast<const __half2*>(&hw));
+            live = !(r0.x < patch.x - h.x) && !(r0.x > patch.z + h.x) && !(r0.y < patch.y - h.y) &&
+                   !(r0.y > patch.w + h.y);
+        }
+        const uint32_t m = __ballot_sync(0xffffffffu, live);
+        if (live) list[n + __popc(m & lt)] = (uint8_t)j;
+        n += __popc(m);
+    }
+    __syncwarp();
+    return n;
+}
+
 // =====================================================================================================
 // forward
 // =====================================================================================================
@@ -61,6 +97,7 @@ render_forward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ranges
     __shared__ __align__(128) float4 s_rec[2][kBatch * 3];
     __shared__ __align__(8) uint64_t s_bar[2];
     __shared__ int s_cnt[2][kBatch];
+    __shared__ uint8_t s_list[SPLAT_TILE_PIXELS / 32][kBatch];
 
     const int tile = blockIdx.x;
     const int tile_x = tile % grid_x, tile_y = tile / grid_x;
@@ -69,7 +106,8 @@ render_forward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ranges
     const bool inside = px < (uint32_t)W && py < (uint32_t)H;
     const uint32_t pix_id = (uint32_t)W * py + px;
     const float pixfx = (float)px, pixfy = (float)py;
-    const uint32_t lane = threadIdx.x & 31;
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const float4 patch = patch_of_warp(tile_x, tile_y);
 
     const uint2 range = ranges[tile];
     const int n = (int)(range.y - range.x);
@@ -98,8 +136,10 @@ render_forward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ranges
         const int cnt = min(kBatch, n - b * kBatch);
         mbar_wait(&s_bar[stage], (uint32_t)((b >> 1) & 1));
         const float4* rec = &s_rec[stage][0];
-        for (int j = 0; j < cnt; ++j) {
+        const int n_live = __all_sync(0xffffffffu, done) ? 0 : bin_batch_for_warp(rec, cnt, patch, s_list[warp], lane);
+        for (int k = 0; k < n_live; ++k) {
             if (__all_sync(0xffffffffu, done)) break;
+            const int j = s_list[warp][k];
             const float4 r0 = rec[3 * j];          // x, y, conic.x, conic.y
             const float4 r1 = rec[3 * j + 1];      // conic.z, opacity, depth, id
             const float dx = fsub(r0.x, pixfx), dy = fsub(r0.y, pixfy);
@@ -216,6 +256,7 @@ render_backward_kernel(int W, int H, int grid_x, const uint2* __restrict__ range
                        const float* __restrict__ dL_dpixels_depth, float* __restrict__ grad_accum) {
     __shared__ __align__(128) float4 s_rec[2][kBatch * 3];
     __shared__ __align__(8) uint64_t s_bar[2];
+    __shared__ uint8_t s_list[SPLAT_TILE_PIXELS / 32][kBatch];
 
     const int tile = blockIdx.x;
     const int tile_x = tile % grid_x, tile_y = tile / grid_x;
@@ -224,7 +265,8 @@ render_backward_kernel(int W, int H, int grid_x, const uint2* __restrict__ range
     const bool inside = px < (uint32_t)W && py < (uint32_t)H;
     const uint32_t pix_id = (uint32_t)W * py + px;
     const float pixfx = (float)px, pixfy = (float)py;
-    const uint32_t lane = threadIdx.x & 31;
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const float4 patch = patch_of_warp(tile_x, tile_y);
 
     const uint2 range = ranges[tile];
     const int n = (int)(range.y - range.x);
@@ -274,7 +316,10 @@ render_backward_kernel(int W, int H, int grid_x, const uint2* __restrict__ range
         mbar_wait(&s_bar[stage], (uint32_t)((b >> 1) & 1));
         const float4* rec = &s_rec[stage][0];
         if (lo < warp_last) {
-            for (int j = min(cnt, warp_last - lo) - 1; j >= 0; --j) {
+            // only list positions below the warp's deepest contributor matter; bin them against the warp's patch
+            const int n_live = bin_batch_for_warp(rec, min(cnt, warp_last - lo), patch, s_list[warp], lane);
+            for (int k = n_live - 1; k >= 0; --k) {
+                const int j = s_list[warp][k];
                 const int idx = lo + j;                        // position in the tile's list
                 const float4 r0 = rec[3 * j];
                 const float4 r1 = rec[3 * j + 1];
