@@ -138,34 +138,32 @@ render_forward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ranges
         const float4* rec = &s_rec[stage][0];
         const int n_live = __all_sync(0xffffffffu, done) ? 0 : bin_batch_for_warp(rec, cnt, patch, s_list[warp], lane);
         for (int k = 0; k < n_live; ++k) {
-            if (__all_sync(0xffffffffu, done)) break;
+            // survivors of the binning almost always touch some lane, so everything up to the blend is evaluated
+            // unconditionally and a single ballot per instance serves both the blend and the n_touched count
             const int j = s_list[warp][k];
             const float4 r0 = rec[3 * j];          // x, y, conic.x, conic.y
             const float4 r1 = rec[3 * j + 1];      // conic.z, opacity, depth, id
             const float dx = fsub(r0.x, pixfx), dy = fsub(r0.y, pixfy);
             const float power = gauss_power_ref(dx, dy, r0.z, r0.w, r1.x);
-            bool act = !done && !(power > 0.0f);
-            if (!__any_sync(0xffffffffu, act)) continue;
             // alpha = min(0.99, opacity * exp(power)); 1/255 cut; transmittance test (forward.cu:350-363)
             const float alpha = fminf(0.99f, fmul(r1.y, expf(power)));
-            act = act && !(alpha < 1.0f / 255.0f);
             const float test_T = fmul(T, fsub(1.0f, alpha));
+            bool act = !done && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
             if (act && test_T < 0.0001f) { done = true; act = false; }
-            if (__any_sync(0xffffffffu, act)) {
+            if (act) {
                 const float4 r2 = rec[3 * j + 2];  // r, g, b
-                if (act) {
-                    // C += c * alpha * T as fma(T, alpha*c, C) (reference SASS order)
-                    C0 = ffma(T, fmul(alpha, r2.x), C0);
-                    C1 = ffma(T, fmul(alpha, r2.y), C1);
-                    C2 = ffma(T, fmul(alpha, r2.z), C2);
-                    Dp = ffma(T, fmul(alpha, r1.z), Dp);
-                    T = test_T;
-                    last_contributor = (uint32_t)(b * kBatch + j + 1);
-                }
-                // n_touched: pixels that blended this Gaussian while still > 50 % transparent (forward.cu:368-370)
-                const uint32_t tv = __ballot_sync(0xffffffffu, act && test_T > 0.5f);
-                if (tv != 0u && lane == 0) atomicAdd(&s_cnt[stage][j], __popc(tv));
+                // C += c * alpha * T as fma(T, alpha*c, C) (reference SASS order)
+                C0 = ffma(T, fmul(alpha, r2.x), C0);
+                C1 = ffma(T, fmul(alpha, r2.y), C1);
+                C2 = ffma(T, fmul(alpha, r2.z), C2);
+                Dp = ffma(T, fmul(alpha, r1.z), Dp);
+                T = test_T;
+                last_contributor = (uint32_t)(b * kBatch + j + 1);
             }
+            // n_touched: pixels that blended this Gaussian while still > 50 % transparent (forward.cu:368-370)
+            const uint32_t tv = __ballot_sync(0xffffffffu, act && test_T > 0.5f);
+            if (tv != 0u && lane == 0) atomicAdd(&s_cnt[stage][j], __popc(tv));
+            if (__all_sync(0xffffffffu, done)) break;
         }
         __syncthreads();   // every warp is done with this stage
         if (threadIdx.x < cnt) {
@@ -325,33 +323,31 @@ render_backward_kernel(int W, int H, int grid_x, const uint2* __restrict__ range
                 const float4 r1 = rec[3 * j + 1];
                 const float dx = fsub(r0.x, pixfx), dy = fsub(r0.y, pixfy);
                 const float power = gauss_power_ref(dx, dy, r0.z, r0.w, r1.x);
-                bool skip = (idx >= last_contributor) || (power > 0.0f);
-                if (__all_sync(0xffffffffu, skip)) continue;
-                const float G = expf(power);
-                const float alpha = fminf(0.99f, fmul(r1.y, G));
-                skip = skip || (alpha < 1.0f / 255.0f);
+                // same expf / alpha as the forward so that the blend decisions replay exactly
+                const float G0 = expf(power);
+                const float alpha0 = fminf(0.99f, fmul(r1.y, G0));
+                const bool skip = (idx >= last_contributor) || (power > 0.0f) || (alpha0 < 1.0f / 255.0f);
                 if (__all_sync(0xffffffffu, skip)) continue;
                 const float4 r2 = rec[3 * j + 2];
-
-                const float one_m_alpha = 1.0f - alpha;
-                const float inv = __frcp_rn(one_m_alpha);
-                T = skip ? T : T * inv;
-                const float dchannel_dcolor = alpha * T;
-                float dL_dalpha;
-                {
-                    const float na0 = last_alpha * lc0 + (1.0f - last_alpha) * acc0;
-                    const float na1 = last_alpha * lc1 + (1.0f - last_alpha) * acc1;
-                    const float na2 = last_alpha * lc2 + (1.0f - last_alpha) * acc2;
-                    const float nad = last_alpha * last_depth + (1.0f - last_alpha) * accd;
-                    acc0 = skip ? acc0 : na0; acc1 = skip ? acc1 : na1; acc2 = skip ? acc2 : na2;
-                    accd = skip ? accd : nad;
-                    lc0 = skip ? lc0 : r2.x; lc1 = skip ? lc1 : r2.y; lc2 = skip ? lc2 : r2.z;
-                    last_depth = skip ? last_depth : r1.z;
-                    dL_dalpha = (r2.x - acc0) * dLp0 + (r2.y - acc1) * dLp1 + (r2.z - acc2) * dLp2 +
-                                (r1.z - accd) * dLpd;
+                // lanes that skip contribute through G = 0 and alpha = 0 (two selects instead of ten)
+                const float G = skip ? 0.0f : G0;
+                const float alpha = skip ? 0.0f : alpha0;
+                float inv;
+                asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(inv) : "f"(1.0f - alpha));
+                if (!skip) {
+                    T = T * inv;
+                    acc0 = last_alpha * lc0 + (1.0f - last_alpha) * acc0;
+                    acc1 = last_alpha * lc1 + (1.0f - last_alpha) * acc1;
+                    acc2 = last_alpha * lc2 + (1.0f - last_alpha) * acc2;
+                    accd = last_alpha * last_depth + (1.0f - last_alpha) * accd;
+                    lc0 = r2.x; lc1 = r2.y; lc2 = r2.z;
+                    last_depth = r1.z;
+                    last_alpha = alpha;
                 }
+                const float dchannel_dcolor = alpha * T;
+                float dL_dalpha = (r2.x - acc0) * dLp0 + (r2.y - acc1) * dLp1 + (r2.z - acc2) * dLp2 +
+                                  (r1.z - accd) * dLpd;
                 dL_dalpha *= T;
-                last_alpha = skip ? last_alpha : alpha;
                 // alpha also scales how much background shows through (backward.cu:736-743)
                 dL_dalpha += (-T_final * inv) * bg_dot_dpixel;
 
@@ -370,8 +366,6 @@ render_backward_kernel(int W, int H, int grid_x, const uint2* __restrict__ range
                 v[7] = dchannel_dcolor * dLp1;
                 v[8] = dchannel_dcolor * dLp2;
                 v[9] = dchannel_dcolor * dLpd;
-#pragma unroll
-                for (int k = 0; k < 10; ++k) v[k] = skip ? 0.0f : v[k];
                 const float total = warp_reduce10(v, lane);
                 if (holder && total != 0.0f) {
                     const uint32_t id = __float_as_uint(r1.w);
