@@ -147,7 +147,7 @@ int splat_raster_forward_render(int P, int R, int W, int H, const float* backgro
         SPLAT_CUDA_CHECK_LAUNCH();
         prof_begin(ST_SORT, s);
         launch_radix_sort(R, passes, b, s);
-        prof_end(ST_SORT, s, 3 * passes);
+        prof_end(ST_SORT, s, passes + 2);
         SPLAT_CUDA_CHECK_LAUNCH();
     }
     prof_begin(ST_RECORDS, s);

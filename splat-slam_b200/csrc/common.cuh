@@ -8,6 +8,7 @@
 // intrinsics (__fmaf_rn/__fmul_rn/__fadd_rn are never re-fused) in the order the reference's sm_100 SASS
 // evaluates them; the comments name the reference expression each sequence reproduces.
 #pragma once
+#include <cuda_fp16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 
@@ -70,6 +71,31 @@ __device__ __forceinline__ float gauss_power_ref(float dx, float dy, float A, fl
 }
 
 __device__ __forceinline__ uint32_t lane_id() { return threadIdx.x & 31u; }
+
+// Conservative axis-aligned half extents (hx, hy), packed as two round-up fp16, of the region where a Gaussian with
+// conic (A, B, C) and opacity o can pass the render kernels' alpha >= 1/255 test: alpha = o*exp(-q(d)) >= 1/255
+// needs q(d) <= tau = ln(255*o), and {q <= tau} with q(d) = 0.5*(A dx^2 + C dy^2) + B dx dy is an ellipse whose
+// bounding box has half widths sqrt(2 tau C/det), sqrt(2 tau A/det). Margins (+0.02 on tau, an anisotropy-scaled
+// widening, x1.001, +0.05 px, fp16 round-up) cover the float rounding of power/expf, so a pixel the reference would
+// blend is never outside the box. Degenerate conics -> "everywhere"; opacity < 1/255 -> "nowhere".
+__device__ __forceinline__ uint32_t footprint_half_extents(float A, float B, float C, float o) {
+    float hx = 65504.0f, hy = 65504.0f;
+    const float tau0 = logf(255.0f * o) + 0.02f;
+    const float det = A * C - B * B;
+    if (tau0 < 0.0f) {
+        hx = hy = -65504.0f;
+    } else if (det > 0.0f && A > 0.0f && C > 0.0f) {
+        // the terms of `power` reach 2*tau*A*C/det near the ellipse, so its float rounding error scales with the
+        // anisotropy A*C/det: widen tau accordingly (negligible for ordinary splats, safe for needle-like ones)
+        const float tau = tau0 * (1.0f + 4e-6f * (A * C / det));
+        const float ex = sqrtf(2.0f * tau * C / det) * 1.001f + 0.05f;
+        const float ey = sqrtf(2.0f * tau * A / det) * 1.001f + 0.05f;
+        if (ex < 65504.0f) hx = ex;
+        if (ey < 65504.0f) hy = ey;
+    }
+    const __half2 h = __halves2half2(__float2half_ru(hx), __float2half_ru(hy));
+    return *reinterpret_cast<const uint32_t*>(&h);
+}
 
 }  // namespace splat
 

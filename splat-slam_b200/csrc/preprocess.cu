@@ -168,16 +168,24 @@ preprocess_forward_kernel(int P, int D, int M,
             get_rect_ref(pim.x, pim.y, my_radius, grid_x, grid_y, x0, y0, x1, y1);
             const uint32_t area = (x1 - x0) * (y1 - y0);
             if (area == 0) break;
+            float3 c;
             if (colors_precomp == nullptr) {
                 uint8_t cb;
-                const float3 c = sh_to_rgb(D, M, shs + (size_t)idx * M * 3, make_float3(px, py, pz),
-                                           make_float3(campos[0], campos[1], campos[2]), cb);
+                c = sh_to_rgb(D, M, shs + (size_t)idx * M * 3, make_float3(px, py, pz),
+                              make_float3(campos[0], campos[1], campos[2]), cb);
                 g.rgb[3 * idx] = c.x; g.rgb[3 * idx + 1] = c.y; g.rgb[3 * idx + 2] = c.z;
                 g.clamped[idx] = cb;
+            } else {
+                c = make_float3(colors_precomp[3 * idx], colors_precomp[3 * idx + 1], colors_precomp[3 * idx + 2]);
             }
             g.depths[idx] = tz;
             g.means2D[idx] = pim;
             g.conic_opacity[idx] = con_o;
+            // everything the render kernels need for this Gaussian, as one 48-byte record
+            g.rec[3 * (size_t)idx + 0] = make_float4(pim.x, pim.y, con_o.x, con_o.y);
+            g.rec[3 * (size_t)idx + 1] = make_float4(con_o.z, con_o.w, tz, __int_as_float(idx));
+            g.rec[3 * (size_t)idx + 2] = make_float4(
+                c.x, c.y, c.z, __uint_as_float(footprint_half_extents(con_o.x, con_o.y, con_o.z, con_o.w)));
             radius_out = my_radius;
             tiles = area;
         } while (false);

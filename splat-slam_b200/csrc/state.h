@@ -38,6 +38,7 @@ struct GeomState {
     float4* conic_opacity;   // [P]   (conic.x, conic.y, conic.z, opacity)
     float* rgb;              // [3P]  SH-evaluated colour (unused when colors_precomp is given)
     float* cov3D;            // [6P]  world covariance (unused when cov3D_precomp is given)
+    float4* rec;             // [3P]  48-byte render record per Gaussian (copied per instance after the sort)
     uint8_t* clamped;        // [P]   bit k set <=> colour channel k was clamped at 0
     uint32_t* tiles_touched; // [P]
     uint32_t* block_sums;    // [nblk+1] per-256-Gaussian-block tile counts, then their exclusive scan
@@ -50,6 +51,7 @@ struct GeomState {
         g.conic_opacity = c.take<float4>(P);
         g.rgb = c.take<float>(3 * P);
         g.cov3D = c.take<float>(6 * P);
+        g.rec = c.take<float4>(3 * P);
         g.clamped = c.take<uint8_t>(P);
         g.tiles_touched = c.take<uint32_t>(P);
         g.block_sums = c.take<uint32_t>((P + kPreBlock - 1) / kPreBlock + 1);
@@ -80,9 +82,14 @@ struct BinningState {
     uint64_t* keys_alt;    // [R] ping-pong buffer
     uint32_t* vals_alt;    // [R]
     float* records;        // [R * SPLAT_REC_FLOATS] per-instance render records in sorted order
-    uint32_t* hist;        // [kRadix * nblk] per-block digit counts of the current pass (digit-major)
-    uint32_t* totals;      // [8 * kRadix] per-pass digit totals
+    uint32_t* totals;      // [8 * kRadix] per-pass global digit histograms, then 8 tile tickets + error flag (64 slots)
+    uint32_t* hist;        // [8][ntiles][kRadix] look-back tile states of the radix-sort passes (directly after totals)
+    static constexpr size_t kTotalsWords = 8 * kRadix + 64;   // 8448 B: keeps `hist` contiguous with `totals`
     static size_t sort_blocks(size_t R) { return (R + kSortTile - 1) / kSortTile; }
+    // bytes of sort scratch that must be zero before a sort with `passes` passes (totals + the used tile states)
+    static size_t sort_scratch_bytes(size_t R, int passes) {
+        return sizeof(uint32_t) * (kTotalsWords + (size_t)passes * sort_blocks(R ? R : 1) * kRadix);
+    }
     static BinningState carve(void* buf, size_t R, size_t* bytes) {
         Carver c(buf);
         BinningState b;
@@ -92,8 +99,8 @@ struct BinningState {
         b.keys_alt = c.take<uint64_t>(Rp);
         b.vals_alt = c.take<uint32_t>(Rp);
         b.records = c.take<float>(Rp * 12);
-        b.hist = c.take<uint32_t>(kRadix * (sort_blocks(Rp) + 1));
-        b.totals = c.take<uint32_t>(8 * kRadix);
+        b.totals = c.take<uint32_t>(kTotalsWords);
+        b.hist = c.take<uint32_t>(8 * kRadix * sort_blocks(Rp));
         if (bytes) *bytes = c.bytes();
         return b;
     }
