@@ -97,6 +97,29 @@ def test_vs_cpu_oracle(name):
     T.compare_vs_cpu_oracle(ours, orc)
 
 
+FULL_SIZE = {
+    # BASELINE.json configs 2/4 (Replica shape), 3 (TUM tracking) and 5 (ScanNet refinement, SH degree 3)
+    "replica_1M_sh0": dict(camera="replica", P=1_000_000, view_k=4),
+    "tum_200k_view7": dict(camera="tum", P=200_000, view_k=7),
+    "scannet_3M_sh3": dict(camera="scannet", P=3_000_000, sh_coeffs=16, sh_degree=3, view_k=2),
+}
+
+
+@needs_ref
+@pytest.mark.parametrize("name", list(FULL_SIZE))
+def test_full_size_bit_exact_and_gradients_vs_reference_extension(name):
+    """The BASELINE.json shapes at full size against the live reference extension."""
+    case = T.make_case(**FULL_SIZE[name])
+    ours = T.ours_forward_with_intermediates(case)
+    ref = T.ref_forward_with_intermediates(T.load_ref(), case)
+    T.compare_intermediates(ours, ref)
+    del ours, ref
+    torch.cuda.empty_cache()
+    a = T.run_module(T.load_ours(), case)
+    b = T.run_module(T.load_ref(), case)
+    T.compare_outputs(a, b, exact_ints=True)
+
+
 # ---- edge cases -------------------------------------------------------------------------------------------
 def test_zero_gaussians():
     m = T.load_ours()
