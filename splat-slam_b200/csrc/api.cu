@@ -11,9 +11,9 @@ inline int grid_dim(int v) { return (v + SPLAT_TILE - 1) / SPLAT_TILE; }
 // ---- diagnostics: kernel-launch counter and optional per-stage CUDA-event timing ------------------------
 enum Stage { ST_PREPROCESS = 0, ST_SCAN, ST_DUP, ST_SORT, ST_RECORDS, ST_RENDER_FWD, ST_ZERO, ST_RENDER_BWD,
              ST_PREPROCESS_BWD, ST_COUNT };
-const char* kStageNames[ST_COUNT] = {"preprocess_forward", "scan_block_sums", "duplicate_with_keys", "radix_sort",
-                                     "ranges_and_records", "render_forward", "zero_grad_scratch", "render_backward",
-                                     "preprocess_backward"};
+const char* kStageNames[ST_COUNT] = {"preprocess_forward", "depth_sort_and_offsets", "duplicate_with_keys",
+                                     "tile_sort", "ranges_and_records", "render_forward", "zero_grad_scratch",
+                                     "render_backward", "preprocess_backward"};
 unsigned long long g_launches = 0;
 int g_prof = 0;
 int g_prof_dev = -1;
@@ -115,8 +115,8 @@ int splat_raster_forward_preprocess(int P, int D, int M, int W, int H, const flo
     prof_end(ST_PREPROCESS, s, 1);
     SPLAT_CUDA_CHECK_LAUNCH();
     prof_begin(ST_SCAN, s);
-    launch_scan_block_sums(P, g, s);
-    prof_end(ST_SCAN, s, 1);
+    launch_depth_sort_and_offsets(P, g, s);   // 2 histogram kernels + 4 sort passes + block sums + scan
+    prof_end(ST_SCAN, s, 8);
     SPLAT_CUDA_CHECK_LAUNCH();
     if (num_rendered_host) {
         cudaError_t e = cudaMemcpyAsync(num_rendered_host, g.num_rendered, sizeof(int), cudaMemcpyDeviceToHost, s);
@@ -136,22 +136,26 @@ int splat_raster_forward_render(int P, int R, int W, int H, const float* backgro
     GeomState g = GeomState::carve(geom, (size_t)P, nullptr);
     BinningState b = BinningState::carve(binning, (size_t)R, nullptr);
     ImageState im = ImageState::carve(image, (size_t)W * H, (size_t)gx * gy, nullptr);
-    const int passes = sort_passes(gx, gy);
+    const int passes = tile_sort_passes(gx, gy);
     if (R > 0) {
-        // unsorted keys go where an odd/even number of ping-pong passes ends in b.keys / b.point_list
-        uint64_t* k0 = (passes & 1) ? b.keys_alt : b.keys;
+        // the ping-pong sort leaves its result in its first buffer pair for an even pass count and in the second
+        // for an odd one: emit the unsorted instances so that the result always lands in b.tkey / b.point_list
+        uint32_t* k0 = (passes & 1) ? b.tkey_alt : b.tkey;
         uint32_t* v0 = (passes & 1) ? b.vals_alt : b.point_list;
+        uint32_t* k1 = (passes & 1) ? b.tkey : b.tkey_alt;
+        uint32_t* v1 = (passes & 1) ? b.point_list : b.vals_alt;
         prof_begin(ST_DUP, s);
         launch_duplicate_with_keys(P, gx, gy, radii, g, k0, v0, s);
         prof_end(ST_DUP, s, 1);
         SPLAT_CUDA_CHECK_LAUNCH();
         prof_begin(ST_SORT, s);
-        launch_radix_sort(R, passes, b, s);
+        launch_sort_pairs(k0, v0, k1, v1, R, passes, b.sort_scratch, s);
         prof_end(ST_SORT, s, passes + 2);
         SPLAT_CUDA_CHECK_LAUNCH();
     }
+    (void)colors_precomp;   // colours were folded into the per-Gaussian record by the preprocess kernel
     prof_begin(ST_RECORDS, s);
-    launch_ranges_and_records(R, gx * gy, colors_precomp, g, b, im.ranges, s);
+    launch_ranges_and_records(R, gx * gy, g, b, im.ranges, s);
     prof_end(ST_RECORDS, s, R > 0 ? 1 : 0);
     SPLAT_CUDA_CHECK_LAUNCH();
     prof_begin(ST_RENDER_FWD, s);

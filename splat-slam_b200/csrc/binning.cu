@@ -1,16 +1,34 @@
-// Binning: instance offsets, (tile|depth) key generation, stable 64-bit LSD radix sort, tile ranges and the
-// gather of per-instance render records.
-// Replaces cub::DeviceScan::InclusiveSum (DGR/cuda_rasterizer/rasterizer_impl.cu:280), duplicateWithKeys (:70-111),
-// getHigherMsb + cub::DeviceRadixSort::SortPairs (:35-50,303-311), cudaMemset + identifyTileRanges (:313-321,116-138).
-#include <cuda_fp16.h>
+// Binning: instance offsets, tile-key generation in depth order, tile ranges and the per-instance render records.
+// Together with radix_sort.cu this replaces cub::DeviceScan::InclusiveSum (DGR/cuda_rasterizer/rasterizer_impl.cu:280),
+// duplicateWithKeys (:70-111), cub::DeviceRadixSort::SortPairs (:303-311), cudaMemset + identifyTileRanges
+// (:313-321,116-138).
 #include "common.cuh"
 #include "kernels.h"
 
 namespace splat {
 
 // ---- offsets -----------------------------------------------------------------------------------------
-// Exclusive scan of the per-block instance counts written by preprocess_forward_kernel; the per-Gaussian
-// offsets themselves never reach HBM (duplicate_with_keys_kernel rebuilds them inside the block).
+// Instance count of every block of 256 Gaussians taken in depth-sorted order.
+__global__ void __launch_bounds__(kPreBlock)
+sorted_block_sums_kernel(int P, const uint32_t* __restrict__ order, const uint32_t* __restrict__ tiles_touched,
+                         uint32_t* __restrict__ block_sums) {
+    __shared__ uint32_t s_warp[kPreBlock / 32];
+    const int i = blockIdx.x * kPreBlock + threadIdx.x;
+    uint32_t v = (i < P) ? tiles_touched[order[i]] : 0u;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    if ((threadIdx.x & 31) == 0) s_warp[threadIdx.x >> 5] = v;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint32_t s = 0;
+#pragma unroll
+        for (int w = 0; w < kPreBlock / 32; ++w) s += s_warp[w];
+        block_sums[blockIdx.x] = s;
+    }
+}
+
+// Exclusive scan of the per-block instance counts; the per-Gaussian offsets themselves never reach HBM
+// (duplicate_with_keys_kernel rebuilds them inside the block).
 __global__ void __launch_bounds__(1024) scan_block_sums_kernel(int nblk, uint32_t* __restrict__ sums,
                                                                uint32_t* __restrict__ total_out) {
     __shared__ uint32_t s_warp[32];
@@ -49,38 +67,41 @@ __global__ void __launch_bounds__(1024) scan_block_sums_kernel(int nblk, uint32_
     if (threadIdx.x == 0) { sums[nblk] = s_carry; total_out[0] = s_carry; }
 }
 
-void launch_scan_block_sums(int P, const GeomState& g, cudaStream_t s) {
+// Depth sort of the Gaussians (4 digit passes over P items, see radix_sort.cu) and the instance offsets in that order.
+void launch_depth_sort_and_offsets(int P, const GeomState& g, cudaStream_t s) {
+    launch_sort_pairs(g.dkey, g.order, g.dkey_alt, g.order_alt, P, 4, g.sort_scratch, s);   // even: result in place
     const int nblk = (P + kPreBlock - 1) / kPreBlock;
+    sorted_block_sums_kernel<<<nblk, kPreBlock, 0, s>>>(P, g.order, g.tiles_touched, g.block_sums);
     scan_block_sums_kernel<<<1, 1024, 0, s>>>(nblk, g.block_sums, g.num_rendered);
 }
 
 // ---- key generation ----------------------------------------------------------------------------------
-// One block per 256 Gaussians. The block rebuilds its local offsets by a shared-memory scan, then ALL threads
-// emit the block's instances cooperatively (instance k -> owner by binary search) so that the 12-byte
-// key/value writes are fully coalesced and a screen-filling Gaussian costs its neighbours nothing.
-// Emission order per Gaussian is row-major over its tile rectangle, as in the reference, so ties under the
-// stable sort resolve identically.
+// One block per 256 Gaussians of the DEPTH-SORTED order. The block rebuilds its local offsets by a shared-memory
+// scan, then ALL threads emit the block's instances cooperatively (instance k -> owner by binary search) so that the
+// 8-byte (tile, id) writes are fully coalesced and a screen-filling Gaussian costs its neighbours nothing.
+// Emission order per Gaussian is row-major over its tile rectangle, as in the reference.
 __global__ void __launch_bounds__(kPreBlock)
 duplicate_with_keys_kernel(int P, int grid_x, int grid_y, const int* __restrict__ radii, GeomState g,
-                           uint64_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out) {
+                           uint32_t* __restrict__ tkeys_out, uint32_t* __restrict__ vals_out) {
     __shared__ uint32_t s_incl[kPreBlock];
-    __shared__ uint32_t s_rect[kPreBlock];   // x0 | y0 << 12 | width << 24 ... widths can reach 4095 -> use two arrays
+    __shared__ uint32_t s_rect[kPreBlock];   // x0 | y0 << 16
     __shared__ uint32_t s_w[kPreBlock];
-    __shared__ uint32_t s_depth[kPreBlock];
+    __shared__ uint32_t s_gid[kPreBlock];
     __shared__ uint32_t s_warp[kPreBlock / 32];
-    const int idx = blockIdx.x * kPreBlock + threadIdx.x;
+    const int i = blockIdx.x * kPreBlock + threadIdx.x;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     uint32_t cnt = 0;
-    if (idx < P) {
-        const int radius = radii[idx];
+    if (i < P) {
+        const uint32_t gid = g.order[i];
+        const int radius = radii[gid];
         if (radius > 0) {
-            const float2 p = g.means2D[idx];
+            const float2 p = g.means2D[gid];
             uint32_t x0, y0, x1, y1;
             get_rect_ref(p.x, p.y, radius, grid_x, grid_y, x0, y0, x1, y1);
             cnt = (x1 - x0) * (y1 - y0);
             s_rect[threadIdx.x] = x0 | (y0 << 16);
             s_w[threadIdx.x] = x1 - x0;
-            s_depth[threadIdx.x] = __float_as_uint(g.depths[idx]);
+            s_gid[threadIdx.x] = gid;
         }
     }
     uint32_t inc = cnt;
@@ -112,44 +133,46 @@ duplicate_with_keys_kernel(int P, int grid_x, int grid_y, const int* __restrict_
         const uint32_t local = k - (s_incl[o] - cnt_o);
         const uint32_t ry = local / w, rx = local - ry * w;
         const uint32_t rect = s_rect[o];
-        const uint32_t tile = ((rect >> 16) + ry) * (uint32_t)grid_x + (rect & 0xffffu) + rx;
-        keys_out[base + k] = ((uint64_t)tile << 32) | (uint64_t)s_depth[o];
-        vals_out[base + k] = (uint32_t)(blockIdx.x * kPreBlock + o);
+        tkeys_out[base + k] = ((rect >> 16) + ry) * (uint32_t)grid_x + (rect & 0xffffu) + rx;
+        vals_out[base + k] = s_gid[o];
     }
 }
 
 void launch_duplicate_with_keys(int P, int grid_x, int grid_y, const int* radii, const GeomState& g,
-                                uint64_t* keys_out, uint32_t* vals_out, cudaStream_t s) {
+                                uint32_t* tkeys_out, uint32_t* vals_out, cudaStream_t s) {
     const int nblk = (P + kPreBlock - 1) / kPreBlock;
-    duplicate_with_keys_kernel<<<nblk, kPreBlock, 0, s>>>(P, grid_x, grid_y, radii, g, keys_out, vals_out);
+    duplicate_with_keys_kernel<<<nblk, kPreBlock, 0, s>>>(P, grid_x, grid_y, radii, g, tkeys_out, vals_out);
 }
 
 // ---- tile ranges + render records --------------------------------------------------------------------
-// One thread per sorted instance: detects tile boundaries (identifyTileRanges) and copies the instance's 48-byte
-// per-Gaussian record {x, y, conic.x, conic.y | conic.z, opacity, depth, id | r, g, b, footprint box} (written by
+// One thread per sorted instance: detects tile boundaries (identifyTileRanges), materialises the reference's 64-bit
+// key (tile << 32 | depth bits) for inspection, and copies the instance's 48-byte per-Gaussian record
+// {x, y, conic.x, conic.y | conic.z, opacity, depth, id | r, g, b, footprint box} (written by
 // preprocess_forward_kernel) into sorted order, so the render kernels stream contiguous records with bulk async
 // copies instead of four dependent gathers per instance.
 __global__ void __launch_bounds__(256)
-ranges_and_records_kernel(int R, const uint64_t* __restrict__ keys, const uint32_t* __restrict__ point_list,
+ranges_and_records_kernel(int R, const uint32_t* __restrict__ tkeys, const uint32_t* __restrict__ point_list,
                           const float4* __restrict__ gauss_rec, uint2* __restrict__ ranges,
-                          float4* __restrict__ records) {
+                          uint64_t* __restrict__ keys64, float4* __restrict__ records) {
     __shared__ float4 s_t[256 / 32][32 * 3];
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     if (i < R) {
-        const uint32_t tile = (uint32_t)(keys[i] >> 32);
+        const uint32_t tile = tkeys[i];
         if (i == 0) {
             ranges[tile].x = 0;
         } else {
-            const uint32_t prev = (uint32_t)(keys[i - 1] >> 32);
+            const uint32_t prev = tkeys[i - 1];
             if (tile != prev) { ranges[prev].y = i; ranges[tile].x = i; }
         }
         if (i == R - 1) ranges[tile].y = R;
         // gather the Gaussian's 48-byte record (three 16-byte loads from one contiguous chunk)
         const float4* src = gauss_rec + 3 * (size_t)point_list[i];
+        const float4 r1 = src[1];
         s_t[warp][lane * 3 + 0] = src[0];
-        s_t[warp][lane * 3 + 1] = src[1];
+        s_t[warp][lane * 3 + 1] = r1;
         s_t[warp][lane * 3 + 2] = src[2];
+        keys64[i] = ((uint64_t)tile << 32) | (uint64_t)__float_as_uint(r1.z);
     }
     __syncwarp();
     // the warp's 32 records are contiguous in the output: write them as three fully coalesced 512-byte rows
@@ -162,12 +185,11 @@ ranges_and_records_kernel(int R, const uint64_t* __restrict__ keys, const uint32
     }
 }
 
-void launch_ranges_and_records(int R, int tiles, const float* colors_precomp, const GeomState& g,
-                               const BinningState& b, uint2* ranges, cudaStream_t s) {
-    (void)colors_precomp;   // colours were folded into the per-Gaussian record by the preprocess kernel
+void launch_ranges_and_records(int R, int tiles, const GeomState& g, const BinningState& b, uint2* ranges,
+                               cudaStream_t s) {
     cudaMemsetAsync(ranges, 0, sizeof(uint2) * (size_t)tiles, s);
     if (R <= 0) return;
-    ranges_and_records_kernel<<<(R + 255) / 256, 256, 0, s>>>(R, b.keys, b.point_list, g.rec, ranges,
+    ranges_and_records_kernel<<<(R + 255) / 256, 256, 0, s>>>(R, b.tkey, b.point_list, g.rec, ranges, b.keys,
                                                               reinterpret_cast<float4*>(b.records));
 }
 

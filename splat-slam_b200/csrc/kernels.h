@@ -32,13 +32,15 @@ void launch_mark_visible(int P, const float* means3D, const float* viewmatrix, b
 // preprocess_bwd.cu
 void launch_preprocess_backward(const BwdParams& p, const GeomState& g, cudaStream_t s);
 // binning.cu
-void launch_scan_block_sums(int P, const GeomState& g, cudaStream_t s);
+void launch_depth_sort_and_offsets(int P, const GeomState& g, cudaStream_t s);
 void launch_duplicate_with_keys(int P, int grid_x, int grid_y, const int* radii, const GeomState& g,
-                                uint64_t* keys_out, uint32_t* vals_out, cudaStream_t s);
-int sort_passes(int grid_x, int grid_y);
-void launch_radix_sort(int R, int passes, const BinningState& b, cudaStream_t s);
-void launch_ranges_and_records(int R, int tiles, const float* colors_precomp, const GeomState& g,
-                               const BinningState& b, uint2* ranges, cudaStream_t s);
+                                uint32_t* tkeys_out, uint32_t* vals_out, cudaStream_t s);
+void launch_ranges_and_records(int R, int tiles, const GeomState& g, const BinningState& b, uint2* ranges,
+                               cudaStream_t s);
+// radix_sort.cu
+int tile_sort_passes(int grid_x, int grid_y);
+void launch_sort_pairs(uint32_t* k0, uint32_t* v0, uint32_t* k1, uint32_t* v1, int n, int passes, uint32_t* scratch,
+                       cudaStream_t s);
 // render.cu
 void launch_render_forward(int W, int H, int grid_x, int grid_y, const uint2* ranges, const float* records,
                            const float* bg, float* final_T, uint32_t* n_contrib, float* out_color, float* out_depth,

@@ -119,13 +119,13 @@ preprocess_forward_kernel(int P, int D, int M,
                           int grid_x, int grid_y, int prefiltered,
                           int* __restrict__ radii, int* __restrict__ n_touched, GeomState g) {
     __shared__ float sV[16], sPm[16];
-    __shared__ uint32_t s_warp_sum[kPreBlock / 32];
     if (threadIdx.x < 16) { sV[threadIdx.x] = viewmatrix[threadIdx.x]; sPm[threadIdx.x] = projmatrix[threadIdx.x]; }
     __syncthreads();
     const int idx = blockIdx.x * kPreBlock + threadIdx.x;
     uint32_t tiles = 0;
     if (idx < P) {
         int radius_out = 0;
+        float tz_out = 0.0f;
         do {
             const float px = means3D[3 * idx], py = means3D[3 * idx + 1], pz = means3D[3 * idx + 2];
             // in_frustum (auxiliary.h:139-164): cull on view-space z only
@@ -188,22 +188,14 @@ preprocess_forward_kernel(int P, int D, int M,
                 c.x, c.y, c.z, __uint_as_float(footprint_half_extents(con_o.x, con_o.y, con_o.z, con_o.w)));
             radius_out = my_radius;
             tiles = area;
+            tz_out = tz;
         } while (false);
         radii[idx] = radius_out;
         n_touched[idx] = 0;
         g.tiles_touched[idx] = tiles;
-    }
-    // per-block instance count for the offset scan (replaces half of cub::DeviceScan, rasterizer_impl.cu:280)
-    uint32_t v = tiles;
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-    if ((threadIdx.x & 31) == 0) s_warp_sum[threadIdx.x >> 5] = v;
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        uint32_t s = 0;
-#pragma unroll
-        for (int w = 0; w < kPreBlock / 32; ++w) s += s_warp_sum[w];
-        g.block_sums[blockIdx.x] = s;
+        // input of the per-Gaussian depth sort (radix_sort.cu): culled Gaussians go to the end
+        g.dkey[idx] = tiles ? __float_as_uint(tz_out) : 0xFFFFFFFFu;
+        g.order[idx] = (uint32_t)idx;
     }
 }
 

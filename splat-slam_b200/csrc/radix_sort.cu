@@ -1,15 +1,22 @@
-// 64-bit (tile | depth) key / 32-bit value radix sort, hand-written for sm_100a.
+// Radix sort of (32-bit key, 32-bit value) pairs, hand-written for sm_100a, and the way it is used to realise the
+// reference's 64-bit (tile | depth) key sort.
 // Replaces getHigherMsb + cub::DeviceRadixSort::SortPairs (DGR/cuda_rasterizer/rasterizer_impl.cu:35-50,303-311).
 //
-// Stable LSD sort with 8-bit digits over the low 32 + ceil(log2(tiles)) key bits only (the reference passes the same
-// end_bit to CUB). "One sweep" structure: one up-front kernel builds the global digit histograms of ALL passes from a
-// single read of the keys; each pass is then ONE kernel that reads its 4096-key tile once, ranks it with
-// warp-synchronous match_any (no atomics), obtains the tile's global digit offsets by decoupled look-back over the
-// preceding tiles' published counts, reorders keys and values through shared memory and writes each digit run with
-// fully coalesced stores. Traffic per pass: 12 B read + 12 B written per instance.
+// The reference sorts R instance keys (tile << 32 | depth bits) with a stable LSD sort over 32 + ceil(log2(tiles))
+// bits. An LSD sort is a sequence of stable passes, low digits first, so it factors exactly:
+//   1. the four depth-digit passes only depend on the Gaussian, not on the instance -> run them ONCE PER GAUSSIAN
+//      (P items instead of R ~ 4P): sort (depth bits, Gaussian id), culled Gaussians keyed 0xFFFFFFFF to the end;
+//   2. emit the instances in that order (duplicate_with_keys_kernel walks the sorted Gaussians);
+//   3. run the remaining tile-digit passes (two for <= 65536 tiles) stably over the R instances.
+// Ties (same tile, same depth bits) resolve by Gaussian index in both formulations, so the resulting point list,
+// keys and tile ranges are bit-identical to the reference's (tests/test_gpu_parity.py).
 //
-// Tiles take their index from an atomic ticket, so a tile only ever waits for tiles that are already resident:
-// the look-back cannot deadlock. A bounded spin turns a would-be hang (e.g. scratch not cleared) into an error flag.
+// Each pass is ONE kernel ("one sweep"): it reads its 4096-pair tile once, ranks it with warp-synchronous match_any
+// (no atomics; keys stay in registers), gets the tile's global digit offsets by decoupled look-back over the
+// preceding tiles' published counts (windows of 16 independent loads), reorders the pairs through shared memory and
+// writes each digit run with coalesced stores. The global digit bases of all passes come from one up-front
+// histogram kernel. Tiles take their index from an atomic ticket, so a tile only waits for tiles that are already
+// resident and the look-back cannot deadlock; a bounded spin turns a would-be hang into an error flag.
 #include "common.cuh"
 #include "kernels.h"
 
@@ -21,7 +28,7 @@ constexpr uint32_t kFlagInc = 2u << 30;   // inclusive prefix (all tiles up to t
 constexpr uint32_t kFlagMask = 3u << 30;
 constexpr uint32_t kValMask = ~kFlagMask;
 constexpr int kWarps = kSortThreads / 32;
-constexpr int kPerWarp = kSortTile / kWarps;   // contiguous keys per warp (512)
+constexpr int kPerWarp = kSortTile / kWarps;   // contiguous pairs per warp (512)
 constexpr int kSteps = kPerWarp / 32;          // 16
 }  // namespace
 
@@ -32,29 +39,25 @@ static int higher_msb(uint32_t n) {
     return msb;
 }
 
-int sort_passes(int grid_x, int grid_y) {
-    const int bits = 32 + higher_msb((uint32_t)(grid_x * grid_y));
-    return (bits + kRadixBits - 1) / kRadixBits;
+int tile_sort_passes(int grid_x, int grid_y) {
+    return (higher_msb((uint32_t)(grid_x * grid_y)) + kRadixBits - 1) / kRadixBits;
 }
 
 // ---- all digit histograms from one read of the keys ------------------------------------------------------
 __global__ void __launch_bounds__(kSortThreads)
-radix_global_hist_kernel(const uint64_t* __restrict__ keys, int R, int passes, uint32_t* __restrict__ ghist) {
-    __shared__ uint32_t s_h[8][kRadix];
-    for (int i = threadIdx.x; i < 8 * kRadix; i += kSortThreads) (&s_h[0][0])[i] = 0;
+radix_global_hist_kernel(const uint32_t* __restrict__ keys, int n, int passes, uint32_t* __restrict__ ghist) {
+    __shared__ uint32_t s_h[4][kRadix];
+    for (int i = threadIdx.x; i < 4 * kRadix; i += kSortThreads) (&s_h[0][0])[i] = 0;
     __syncthreads();
-    // keys arrive in emission order (by Gaussian), so neighbouring lanes rarely share a digit: plain shared-memory
-    // atomics beat warp aggregation here; four keys per thread in flight hide the load latency
     const int stride = (int)gridDim.x * kSortThreads;
-    for (int base = (int)blockIdx.x * kSortThreads + (int)threadIdx.x; base < R; base += 4 * stride) {
-        uint64_t k[4];
+    for (int base = (int)blockIdx.x * kSortThreads + (int)threadIdx.x; base < n; base += 4 * stride) {
+        uint32_t k[4];
 #pragma unroll
-        for (int u = 0; u < 4; ++u) k[u] = (base + u * stride < R) ? keys[base + u * stride] : 0ull;
+        for (int u = 0; u < 4; ++u) k[u] = (base + u * stride < n) ? keys[base + u * stride] : 0u;
 #pragma unroll
         for (int u = 0; u < 4; ++u) {
-            if (base + u * stride < R) {
-                for (int p = 0; p < passes; ++p)
-                    atomicAdd(&s_h[p][(uint32_t)(k[u] >> (p * kRadixBits)) & (kRadix - 1)], 1u);
+            if (base + u * stride < n) {
+                for (int p = 0; p < passes; ++p) atomicAdd(&s_h[p][(k[u] >> (p * kRadixBits)) & (kRadix - 1)], 1u);
             }
         }
     }
@@ -87,14 +90,13 @@ __global__ void __launch_bounds__(kRadix) radix_global_scan_kernel(uint32_t* __r
 
 // ---- one pass ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(kSortThreads)
-radix_onesweep_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
-                      uint64_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out, int R, int shift,
+radix_onesweep_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
+                      uint32_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out, int n, int shift,
                       const uint32_t* __restrict__ gbase, uint32_t* tile_state, uint32_t* ticket,
                       uint32_t* error_flag, int ntiles) {
-    __shared__ uint32_t s_cnt[kWarps][kRadix];     // per-warp digit counts -> per-warp local positions
-    __shared__ __align__(16) uint64_t s_keys[kSortTile];   // reorder buffer (keys, then reused for values)
-    __shared__ uint32_t s_goff[kRadix];            // global offset of the digit run minus its local base
-    __shared__ uint8_t s_dig[kSortTile];           // digit of each reordered slot (for the value pass)
+    __shared__ uint32_t s_cnt[kWarps][kRadix];       // per-warp digit counts -> per-warp local positions
+    __shared__ __align__(16) uint2 s_kv[kSortTile];  // reorder buffer (key, value)
+    __shared__ uint32_t s_goff[kRadix];              // global offset of the digit run minus its local base
     __shared__ uint32_t s_scan[kWarps];
     __shared__ uint32_t s_tile;
 
@@ -106,22 +108,26 @@ radix_onesweep_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* __re
     if (tile >= ntiles) return;
     const int wbase = tile * kSortTile + warp * kPerWarp;
 
-    // rank: keys stay in registers; rank[st] = number of earlier keys of this warp with the same digit
-    uint64_t key[kSteps];
-    uint32_t rank[kSteps];
-    const uint32_t lt = (1u << lane) - 1u;
-    // all 16 loads are issued before the ranking loop: __syncwarp() in that loop is a memory barrier and would
+    // all loads are issued before the ranking loop: __syncwarp() in that loop is a memory barrier and would
     // otherwise serialise one global round trip per step
+    uint32_t key[kSteps], val[kSteps], rank[kSteps];
 #pragma unroll
     for (int st = 0; st < kSteps; ++st) {
         const int idx = wbase + st * 32 + lane;
-        key[st] = (idx < R) ? keys_in[idx] : 0ull;
+        key[st] = (idx < n) ? keys_in[idx] : 0u;
     }
 #pragma unroll
     for (int st = 0; st < kSteps; ++st) {
         const int idx = wbase + st * 32 + lane;
-        const bool valid = idx < R;
-        const uint32_t d = valid ? (uint32_t)(key[st] >> shift) & (kRadix - 1) : (uint32_t)kRadix;
+        val[st] = (idx < n) ? vals_in[idx] : 0u;
+    }
+    // rank[st] = number of earlier keys of this warp with the same digit (stable within the warp's chunk)
+    const uint32_t lt = (1u << lane) - 1u;
+#pragma unroll
+    for (int st = 0; st < kSteps; ++st) {
+        const int idx = wbase + st * 32 + lane;
+        const bool valid = idx < n;
+        const uint32_t d = valid ? (key[st] >> shift) & (kRadix - 1) : (uint32_t)kRadix;
         const uint32_t peers = __match_any_sync(0xffffffffu, d);
         const int leader = __ffs(peers) - 1;
         uint32_t prev = 0;
@@ -144,8 +150,8 @@ radix_onesweep_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* __re
     } else {
         state[d] = c | kFlagAgg;
         // Look back kLook predecessors at a time: the loads are independent, so a window costs one L2 round trip
-        // instead of kLook. (When a whole wave of tiles starts together none of them has an inclusive prefix yet and
-        // the walk is hundreds of tiles long; one dependent load per tile made that walk the cost of the pass.)
+        // instead of kLook (when a whole wave of tiles starts together none has an inclusive prefix yet and the walk
+        // is hundreds of tiles long).
         constexpr int kLook = 16;
         bool found = false;
         for (int t = tile - 1; t >= 0 && !found; t -= kLook) {
@@ -189,67 +195,49 @@ radix_onesweep_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* __re
     for (int w = 0; w < kWarps; ++w) s_cnt[w][d] += local_base;
     __syncthreads();
 
-    // reorder keys through shared memory; rank[] becomes the local slot
+    // reorder the pairs through shared memory, then write the digit runs with coalesced stores
 #pragma unroll
     for (int st = 0; st < kSteps; ++st) {
         const int idx = wbase + st * 32 + lane;
-        if (idx < R) {
-            const uint32_t dg = (uint32_t)(key[st] >> shift) & (kRadix - 1);
-            const uint32_t pos = s_cnt[warp][dg] + rank[st];
-            rank[st] = pos;
-            s_keys[pos] = key[st];
+        if (idx < n) {
+            const uint32_t dg = (key[st] >> shift) & (kRadix - 1);
+            s_kv[s_cnt[warp][dg] + rank[st]] = make_uint2(key[st], val[st]);
         }
     }
     __syncthreads();
-    const int n_valid = min(kSortTile, R - tile * kSortTile);
+    const int n_valid = min(kSortTile, n - tile * kSortTile);
     for (int i = threadIdx.x; i < n_valid; i += kSortThreads) {
-        const uint64_t k = s_keys[i];
-        const uint32_t dg = (uint32_t)(k >> shift) & (kRadix - 1);
-        s_dig[i] = (uint8_t)dg;
-        keys_out[s_goff[dg] + i] = k;
+        const uint2 kv = s_kv[i];
+        const uint32_t pos = s_goff[(kv.x >> shift) & (kRadix - 1)] + i;
+        keys_out[pos] = kv.x;
+        vals_out[pos] = kv.y;
     }
-    __syncthreads();
-    uint32_t* s_vals = reinterpret_cast<uint32_t*>(s_keys);
-#pragma unroll
-    for (int st = 0; st < kSteps; ++st) {
-        const int idx = wbase + st * 32 + lane;
-        if (idx < R) s_vals[rank[st]] = vals_in[idx];
-    }
-    __syncthreads();
-    for (int i = threadIdx.x; i < n_valid; i += kSortThreads) vals_out[s_goff[s_dig[i]] + i] = s_vals[i];
 }
 
-// Sorts (b.keys_alt/b.vals_alt or b.keys/b.point_list, whichever the key generation filled for this pass count) so
-// that the result always lands in b.keys / b.point_list.
-void launch_radix_sort(int R, int passes, const BinningState& b, cudaStream_t s) {
-    if (R <= 0) return;
-    const int ntiles = (int)BinningState::sort_blocks((size_t)R);
-    // scratch: [8][256] digit histograms, [8] tickets + error flag, then [passes][ntiles][256] tile states
-    cudaMemsetAsync(b.totals, 0, BinningState::sort_scratch_bytes((size_t)R, passes), s);
-    uint32_t* ghist = b.totals;
-    uint32_t* tickets = b.totals + 8 * kRadix;
+// Stable LSD sort of n (key, value) pairs on key bits [0, 8*passes). Ping-pongs between (k0, v0) and (k1, v1): the
+// input is read from (k0, v0); the result lands in (k0, v0) for an even pass count and in (k1, v1) for an odd one.
+// scratch: SortScratch::words(n) zero-initialised-by-us 32-bit words.
+void launch_sort_pairs(uint32_t* k0, uint32_t* v0, uint32_t* k1, uint32_t* v1, int n, int passes, uint32_t* scratch,
+                       cudaStream_t s) {
+    if (n <= 0 || passes <= 0) return;
+    const int ntiles = (n + kSortTile - 1) / kSortTile;
+    // scratch: [4][256] digit histograms, [4] tickets, error flag (64 words), then [passes][ntiles][256] tile states
+    cudaMemsetAsync(scratch, 0, sizeof(uint32_t) * (4 * kRadix + 64 + (size_t)passes * ntiles * kRadix), s);
+    uint32_t* ghist = scratch;
+    uint32_t* tickets = scratch + 4 * kRadix;
     uint32_t* error_flag = tickets + 8;
-    uint32_t* states = b.hist;
+    uint32_t* states = scratch + 4 * kRadix + 64;
     const int hist_blocks = ntiles < 592 ? ntiles : 592;   // 148 SMs x 4
-    const int sweep_blocks = ntiles;                       // tiles take their index from the ticket, not blockIdx
-    radix_global_hist_kernel<<<hist_blocks, kSortThreads, 0, s>>>(
-        (passes & 1) ? b.keys_alt : b.keys, R, passes, ghist);
+    radix_global_hist_kernel<<<hist_blocks, kSortThreads, 0, s>>>(k0, n, passes, ghist);
     radix_global_scan_kernel<<<passes, kRadix, 0, s>>>(ghist);
-    // with an odd pass count the unsorted input starts in the alt buffers, with an even count in the main ones
-    uint64_t* kin = (passes & 1) ? b.keys_alt : b.keys;
-    uint32_t* vin = (passes & 1) ? b.vals_alt : b.point_list;
-    uint64_t* kout = (passes & 1) ? b.keys : b.keys_alt;
-    uint32_t* vout = (passes & 1) ? b.point_list : b.vals_alt;
+    uint32_t *kin = k0, *vin = v0, *kout = k1, *vout = v1;
     for (int p = 0; p < passes; ++p) {
-        radix_onesweep_kernel<<<sweep_blocks, kSortThreads, 0, s>>>(kin, vin, kout, vout, R, p * kRadixBits,
-                                                                   ghist + p * kRadix,
-                                                                   states + (size_t)p * ntiles * kRadix, tickets + p,
-                                                                   error_flag, ntiles);
-        uint64_t* tk = kin; kin = kout; kout = tk;
+        radix_onesweep_kernel<<<ntiles, kSortThreads, 0, s>>>(kin, vin, kout, vout, n, p * kRadixBits,
+                                                             ghist + p * kRadix, states + (size_t)p * ntiles * kRadix,
+                                                             tickets + p, error_flag, ntiles);
+        uint32_t* tk = kin; kin = kout; kout = tk;
         uint32_t* tv = vin; vin = vout; vout = tv;
     }
 }
-
-int radix_sort_kernel_count(int passes) { return passes + 2; }
 
 }  // namespace splat

@@ -2,8 +2,8 @@
 // The reference bump-allocates GeometryState / ImageState / BinningState out of byte tensors
 // (DGR/cuda_rasterizer/rasterizer_impl.h:21-73, rasterizer_impl.cu:155-194); the layout is private to the
 // library, so this build uses its own: SoA arrays sized for coalesced access, 256-B aligned sub-arrays,
-// and all scratch (scan partials, radix-sort histograms) carved from the same caller-owned buffers so the
-// library never allocates device memory.
+// and all scratch (scan partials, radix-sort histograms and look-back states) carved from the same caller-owned
+// buffers so the library never allocates device memory.
 #pragma once
 #include <cuda_runtime.h>
 #include <stddef.h>
@@ -12,11 +12,18 @@
 namespace splat {
 
 constexpr int kPreBlock = 256;       // Gaussians per preprocess / duplicate block
-constexpr int kSortItems = 16;       // keys per thread in the radix-sort kernels
+constexpr int kSortItems = 16;       // pairs per thread in the radix-sort kernels
 constexpr int kSortThreads = 256;
-constexpr int kSortTile = kSortItems * kSortThreads;  // 4096 keys per block
+constexpr int kSortTile = kSortItems * kSortThreads;  // 4096 pairs per block
 constexpr int kRadixBits = 8;
 constexpr int kRadix = 1 << kRadixBits;
+
+// 32-bit words of scratch launch_sort_pairs needs for n pairs and up to 4 passes:
+// [4][256] digit histograms + 64 (tickets, error flag) + [4][ntiles][256] look-back tile states
+inline size_t sort_scratch_words(size_t n) {
+    const size_t ntiles = (n + kSortTile - 1) / kSortTile;
+    return 4 * kRadix + 64 + 4 * (ntiles ? ntiles : 1) * kRadix;
+}
 
 struct Carver {
     char* base;
@@ -33,7 +40,7 @@ struct Carver {
 };
 
 struct GeomState {
-    float* depths;           // [P]   view-space z (its bit pattern is the low half of the sort key)
+    float* depths;           // [P]   view-space z (its bit pattern is the low half of the reference's sort key)
     float2* means2D;         // [P]   pixel-space centre
     float4* conic_opacity;   // [P]   (conic.x, conic.y, conic.z, opacity)
     float* rgb;              // [3P]  SH-evaluated colour (unused when colors_precomp is given)
@@ -41,7 +48,12 @@ struct GeomState {
     float4* rec;             // [3P]  48-byte render record per Gaussian (copied per instance after the sort)
     uint8_t* clamped;        // [P]   bit k set <=> colour channel k was clamped at 0
     uint32_t* tiles_touched; // [P]
-    uint32_t* block_sums;    // [nblk+1] per-256-Gaussian-block tile counts, then their exclusive scan
+    uint32_t* dkey;          // [P]   depth bits (0xFFFFFFFF for culled Gaussians) -> sorted
+    uint32_t* order;         // [P]   Gaussian ids -> ids in (depth, id) order
+    uint32_t* dkey_alt;      // [P]   ping-pong buffers of the depth sort
+    uint32_t* order_alt;     // [P]
+    uint32_t* sort_scratch;  // [sort_scratch_words(P)]
+    uint32_t* block_sums;    // [nblk+1] instance counts per 256 depth-sorted Gaussians, then their exclusive scan
     uint32_t* num_rendered;  // [1]   R = total instances (device copy)
     static GeomState carve(void* buf, size_t P, size_t* bytes) {
         Carver c(buf);
@@ -54,6 +66,11 @@ struct GeomState {
         g.rec = c.take<float4>(3 * P);
         g.clamped = c.take<uint8_t>(P);
         g.tiles_touched = c.take<uint32_t>(P);
+        g.dkey = c.take<uint32_t>(P);
+        g.order = c.take<uint32_t>(P);
+        g.dkey_alt = c.take<uint32_t>(P);
+        g.order_alt = c.take<uint32_t>(P);
+        g.sort_scratch = c.take<uint32_t>(sort_scratch_words(P));
         g.block_sums = c.take<uint32_t>((P + kPreBlock - 1) / kPreBlock + 1);
         g.num_rendered = c.take<uint32_t>(4);
         if (bytes) *bytes = c.bytes();
@@ -77,30 +94,24 @@ struct ImageState {
 };
 
 struct BinningState {
-    uint64_t* keys;        // [R] sorted (tile << 32 | depth bits)
-    uint32_t* point_list;  // [R] sorted Gaussian ids
-    uint64_t* keys_alt;    // [R] ping-pong buffer
-    uint32_t* vals_alt;    // [R]
-    float* records;        // [R * SPLAT_REC_FLOATS] per-instance render records in sorted order
-    uint32_t* totals;      // [8 * kRadix] per-pass global digit histograms, then 8 tile tickets + error flag (64 slots)
-    uint32_t* hist;        // [8][ntiles][kRadix] look-back tile states of the radix-sort passes (directly after totals)
-    static constexpr size_t kTotalsWords = 8 * kRadix + 64;   // 8448 B: keeps `hist` contiguous with `totals`
-    static size_t sort_blocks(size_t R) { return (R + kSortTile - 1) / kSortTile; }
-    // bytes of sort scratch that must be zero before a sort with `passes` passes (totals + the used tile states)
-    static size_t sort_scratch_bytes(size_t R, int passes) {
-        return sizeof(uint32_t) * (kTotalsWords + (size_t)passes * sort_blocks(R ? R : 1) * kRadix);
-    }
+    uint64_t* keys;          // [R] sorted (tile << 32 | depth bits), materialised after the sort for inspection
+    uint32_t* point_list;    // [R] sorted Gaussian ids
+    uint32_t* tkey;          // [R] tile id per instance -> sorted
+    uint32_t* tkey_alt;      // [R] ping-pong buffers of the tile sort
+    uint32_t* vals_alt;      // [R]
+    float* records;          // [R * SPLAT_REC_FLOATS] per-instance render records in sorted order
+    uint32_t* sort_scratch;  // [sort_scratch_words(R)]
     static BinningState carve(void* buf, size_t R, size_t* bytes) {
         Carver c(buf);
         BinningState b;
         const size_t Rp = R ? R : 1;
         b.keys = c.take<uint64_t>(Rp);
         b.point_list = c.take<uint32_t>(Rp);
-        b.keys_alt = c.take<uint64_t>(Rp);
+        b.tkey = c.take<uint32_t>(Rp);
+        b.tkey_alt = c.take<uint32_t>(Rp);
         b.vals_alt = c.take<uint32_t>(Rp);
         b.records = c.take<float>(Rp * 12);
-        b.totals = c.take<uint32_t>(kTotalsWords);
-        b.hist = c.take<uint32_t>(8 * kRadix * sort_blocks(Rp));
+        b.sort_scratch = c.take<uint32_t>(sort_scratch_words(Rp));
         if (bytes) *bytes = c.bytes();
         return b;
     }
