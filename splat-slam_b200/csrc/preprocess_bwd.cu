@@ -103,7 +103,7 @@ __device__ f3 sh_backward(int deg, int M, const float* __restrict__ shs, f3 pos,
     return dnormvdv(dir_orig, dL_ddir);
 }
 
-__global__ void __launch_bounds__(kPreBlock)
+__global__ void __launch_bounds__(kPreBlock, 4)
 preprocess_backward_kernel(BwdParams p, GeomState g, float* __restrict__ tau_partial) {
     __shared__ float sV[16], sPm[16];
     __shared__ float s_tau[kPreBlock / 32][6];

@@ -89,7 +89,7 @@ __global__ void __launch_bounds__(kRadix) radix_global_scan_kernel(uint32_t* __r
 }
 
 // ---- one pass ---------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(kSortThreads)
+__global__ void __launch_bounds__(kSortThreads, 3)
 radix_onesweep_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
                       uint32_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out, int n, int shift,
                       const uint32_t* __restrict__ gbase, uint32_t* tile_state, uint32_t* ticket,
