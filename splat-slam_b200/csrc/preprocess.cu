@@ -4,6 +4,7 @@
 #include <cstdio>
 #include "common.cuh"
 #include "kernels.h"
+#include "project.cuh"
 
 namespace splat {
 
@@ -46,66 +47,6 @@ __device__ __forceinline__ float3 sh_to_rgb(int deg, int M, const float* __restr
     r.x += 0.5f; r.y += 0.5f; r.z += 0.5f;
     clamp_bits = (r.x < 0.0f ? 1 : 0) | (r.y < 0.0f ? 2 : 0) | (r.z < 0.0f ? 4 : 0);
     return make_float3(fmaxf(r.x, 0.0f), fmaxf(r.y, 0.0f), fmaxf(r.z, 0.0f));
-}
-
-// Sigma = (S R)^T (S R) from scale and the UN-normalised quaternion (r,x,y,z) (DGR forward.cu:120-154).
-// Rounding sequence reproduces the reference SASS: six cross terms are fma(u,v,+-(w*t)) with the rounded
-// product being r*z, x*z and r*x respectively; squares are y*y, z*z rounded and x*x fused.
-__device__ __forceinline__ void cov3d_ref(float sx, float sy, float sz, float mod, float4 q, float* cov) {
-    const float r = q.x, x = q.y, y = q.z, z = q.w;
-    const float yy = fmul(y, y), zz = fmul(z, z);
-    const float rz = fmul(r, z), xz = fmul(x, z), rx = fmul(r, x);
-    const float xy_m_rz = ffma(x, y, -rz), xy_p_rz = ffma(x, y, rz);
-    const float xz_p_ry = ffma(r, y, xz), xz_m_ry = ffma(-r, y, xz);
-    const float yz_m_rx = ffma(y, z, -rx), yz_p_rx = ffma(y, z, rx);
-    const float xx_zz = ffma(x, x, zz), xx_yy = ffma(x, x, yy), yy_zz = fadd(yy, zz);
-    // rotation rows in the order the reference passes them to glm::mat3 (as columns)
-    const float R00 = fsub(1.0f, fadd(yy_zz, yy_zz)), R01 = fadd(xy_m_rz, xy_m_rz), R02 = fadd(xz_p_ry, xz_p_ry);
-    const float R10 = fadd(xy_p_rz, xy_p_rz), R11 = fsub(1.0f, fadd(xx_zz, xx_zz)), R12 = fadd(yz_m_rx, yz_m_rx);
-    const float R20 = fadd(xz_m_ry, xz_m_ry), R21 = fadd(yz_p_rx, yz_p_rx), R22 = fsub(1.0f, fadd(xx_yy, xx_yy));
-    const float s0 = fmul(mod, sx), s1 = fmul(mod, sy), s2 = fmul(mod, sz);
-    // M (glm) column c = s (.) R-row c
-    const float m00 = fmul(s0, R00), m01 = fmul(s1, R01), m02 = fmul(s2, R02);
-    const float m10 = fmul(s0, R10), m11 = fmul(s1, R11), m12 = fmul(s2, R12);
-    const float m20 = fmul(s0, R20), m21 = fmul(s1, R21), m22 = fmul(s2, R22);
-    cov[0] = dot3_ref(m00, m00, m01, m01, m02, m02);
-    cov[1] = dot3_ref(m10, m00, m11, m01, m12, m02);
-    cov[2] = dot3_ref(m20, m00, m21, m01, m22, m02);
-    cov[3] = dot3_ref(m10, m10, m11, m11, m12, m12);
-    cov[4] = dot3_ref(m20, m10, m21, m11, m22, m12);
-    cov[5] = dot3_ref(m20, m20, m21, m21, m22, m22);
-}
-
-// EWA projection of the 3D covariance with the 1.3*tanfov guard band and the 0.3 low-pass
-// (DGR forward.cu:76-115). t = view-space mean (already computed, identical ops). Returns (a, b, c).
-__device__ __forceinline__ float3 cov2d_ref(float tx, float ty, float tz, float fx, float fy, float tanfovx,
-                                            float tanfovy, const float* cov, const float* __restrict__ V) {
-    const float limx = fmul(tanfovx, 1.3f), limy = fmul(tanfovy, 1.3f);
-    const float txtz = __fdiv_rn(tx, tz), tytz = __fdiv_rn(ty, tz);
-    const float cxl = fminf(limx, fmaxf(-limx, txtz));
-    const float cyl = fminf(limy, fmaxf(-limy, tytz));
-    const float tz2 = fmul(tz, tz);
-    const float J00 = __fdiv_rn(fx, tz);
-    const float J02 = __fdiv_rn(fmul(fx, fmul(cxl, -tz)), tz2);
-    const float J11 = __fdiv_rn(fy, tz);
-    const float J12 = __fdiv_rn(fmul(fy, fmul(cyl, -tz)), tz2);
-    float T0[3], T1[3];
-#pragma unroll
-    for (int r = 0; r < 3; ++r) {
-        T0[r] = ffma(V[4 * r + 2], J02, fmul(V[4 * r], J00));
-        T1[r] = ffma(V[4 * r + 2], J12, fmul(J11, V[4 * r + 1]));
-    }
-    const float v0[3] = {cov[0], cov[1], cov[2]}, v1[3] = {cov[1], cov[3], cov[4]}, v2[3] = {cov[2], cov[4], cov[5]};
-    const float X00 = dot3_ref(T0[0], v0[0], T0[1], v0[1], T0[2], v0[2]);
-    const float X01 = dot3_ref(T1[0], v0[0], T1[1], v0[1], T1[2], v0[2]);
-    const float X10 = dot3_ref(T0[0], v1[0], T0[1], v1[1], T0[2], v1[2]);
-    const float X11 = dot3_ref(T1[0], v1[0], T1[1], v1[1], T1[2], v1[2]);
-    const float X20 = dot3_ref(T0[0], v2[0], T0[1], v2[1], T0[2], v2[2]);
-    const float X21 = dot3_ref(T1[0], v2[0], T1[1], v2[1], T1[2], v2[2]);
-    const float c00 = dot3_ref(T0[0], X00, T0[1], X10, T0[2], X20);
-    const float c01 = dot3_ref(T0[0], X01, T0[1], X11, T0[2], X21);
-    const float c11 = dot3_ref(T1[0], X01, T1[1], X11, T1[2], X21);
-    return make_float3(fadd(c00, 0.3f), c01, fadd(c11, 0.3f));
 }
 
 __global__ void __launch_bounds__(kPreBlock)
@@ -151,7 +92,8 @@ preprocess_forward_kernel(int P, int D, int M,
 #pragma unroll
                 for (int k = 0; k < 6; ++k) g.cov3D[6 * idx + k] = cov[k];
             }
-            const float3 abc = cov2d_ref(tx, ty, tz, focal_x, focal_y, tanfovx, tanfovy, cov, sV);
+            const EwaRef ewa = ewa_ref(tx, ty, tz, focal_x, focal_y, tanfovx, tanfovy, cov, sV);
+            const float3 abc = make_float3(ewa.a, ewa.b, ewa.c);
             // det = a*c - b*b as fma(a, c, -(b*b)); conic = inverse (forward.cu:216-221)
             const float det = ffma(abc.x, abc.z, -fmul(abc.y, abc.y));
             if (det == 0.0f) break;

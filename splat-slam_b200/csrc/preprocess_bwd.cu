@@ -9,6 +9,7 @@
 // render-gradient accumulator, which backward render fills with atomics, is cleared beforehand.
 #include "common.cuh"
 #include "kernels.h"
+#include "project.cuh"
 
 namespace splat {
 
@@ -125,28 +126,28 @@ preprocess_backward_kernel(BwdParams p, GeomState g, float* __restrict__ tau_par
             const float* cov3D = p.cov3D_precomp ? p.cov3D_precomp + 6 * (size_t)idx : g.cov3D + 6 * (size_t)idx;
 
             // ---------------- conic -> cov2D -> cov3D / t / W  (backward.cu:150-346) ----------------
-            f3 t = mk(sV[0] * m.x + sV[4] * m.y + sV[8] * m.z + sV[12], sV[1] * m.x + sV[5] * m.y + sV[9] * m.z + sV[13],
-                      sV[2] * m.x + sV[6] * m.y + sV[10] * m.z + sV[14]);
+            // view-space mean, guard-band clamp, Jacobian, A = J W and (a, b, c): the forward's own bit-exact sequence
+            f3 t = mk(affine_row_ref(m.x, m.y, m.z, sV[0], sV[4], sV[8], sV[12]),
+                      affine_row_ref(m.x, m.y, m.z, sV[1], sV[5], sV[9], sV[13]),
+                      affine_row_ref(m.x, m.y, m.z, sV[2], sV[6], sV[10], sV[14]));
             const f3 p_C = t;   // unclamped camera-frame point, used by the mean2D/depth pose terms below
-            const float limx = 1.3f * p.tanfovx, limy = 1.3f * p.tanfovy;
-            const float txtz = t.x / t.z, tytz = t.y / t.z;
-            t.x = fminf(limx, fmaxf(-limx, txtz)) * t.z;
-            t.y = fminf(limy, fmaxf(-limy, tytz)) * t.z;
-            const float x_grad_mul = (txtz < -limx || txtz > limx) ? 0.0f : 1.0f;
-            const float y_grad_mul = (tytz < -limy || tytz > limy) ? 0.0f : 1.0f;
             const float hx = p.focal_x, hy = p.focal_y;
-            const float J00 = hx / t.z, J02 = -(hx * t.x) / (t.z * t.z);
-            const float J11 = hy / t.z, J12 = -(hy * t.y) / (t.z * t.z);
+            const EwaRef e = ewa_ref(t.x, t.y, t.z, hx, hy, p.tanfovx, p.tanfovy, cov3D, sV);
+            t.x = e.txc;
+            t.y = e.tyc;
+            const float x_grad_mul = (e.txtz < -e.limx || e.txtz > e.limx) ? 0.0f : 1.0f;
+            const float y_grad_mul = (e.tytz < -e.limy || e.tytz > e.limy) ? 0.0f : 1.0f;
+            const float J00 = e.J00, J02 = e.J02, J11 = e.J11, J12 = e.J12;
             // rows of the world->camera rotation: R(i,k) = view[4k+i]
             const f3 R0 = mk(sV[0], sV[4], sV[8]), R1 = mk(sV[1], sV[5], sV[9]), R2 = mk(sV[2], sV[6], sV[10]);
-            const f3 A0 = J00 * R0 + J02 * R2;     // A = J R, rows 0 and 1
-            const f3 A1 = J11 * R1 + J12 * R2;
+            const f3 A0 = mk(e.T0[0], e.T0[1], e.T0[2]);     // A = J R, rows 0 and 1
+            const f3 A1 = mk(e.T1[0], e.T1[1], e.T1[2]);
             const f3 V0 = mk(cov3D[0], cov3D[1], cov3D[2]), V1 = mk(cov3D[1], cov3D[3], cov3D[4]),
                      V2 = mk(cov3D[2], cov3D[4], cov3D[5]);
             const f3 VA0 = mk(dot(V0, A0), dot(V1, A0), dot(V2, A0));
             const f3 VA1 = mk(dot(V0, A1), dot(V1, A1), dot(V2, A1));
-            const float a = dot(A0, VA0) + 0.3f, b = dot(A0, VA1), c = dot(A1, VA1) + 0.3f;
-            const float denom = a * c - b * b;
+            const float a = e.a, b = e.b, c = e.c;
+            const float denom = ffma(a, c, -fmul(b, b));
             const float denom2inv = 1.0f / ((denom * denom) + 0.0000001f);
             const float gx = acc0.z, gy = acc0.w, gz = acc1.x;   // dL_dconic slots [0],[1],[3]
             float dL_da = 0, dL_db = 0, dL_dc = 0;
