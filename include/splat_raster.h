@@ -74,7 +74,10 @@ int splat_raster_forward_render(
  *                     (DGR/diff_gaussian_rasterization/__init__.py:152-154)
  * All other outputs are fully written, zeros for culled Gaussians: dL_dmeans2D[P*3], dL_dcolors[P*3],
  * dL_dopacity[P], dL_dmeans3D[P*3], dL_dcov3D[P*6], dL_dsh[P*M*3] (if shs), dL_dscales[P*3] and
- * dL_drotations[P*4] (if scales). */
+ * dL_drotations[P*4] (if scales). Any of these eight may be NULL when the caller does not need it (the reference
+ * always computes all of them, DGR/diff_gaussian_rasterization/__init__.py:107-171 has no needs_input_grad check);
+ * a pose-only tracking step passes NULL for all of them. Exceptions: dL_dscales/dL_drotations come as a pair, and
+ * dL_dsh is required when D > 0 because the SH direction term also feeds the pose gradient (backward.cu:141-143). */
 int splat_raster_backward(
     int P, int D, int M, int R, int W, int H,
     const float* background, const float* means3D, const float* shs, const float* colors_precomp,

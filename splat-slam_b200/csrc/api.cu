@@ -178,11 +178,11 @@ int splat_raster_backward(int P, int D, int M, int R, int W, int H, const float*
     if (P < 0 || R < 0 || W <= 0 || H <= 0 || D < 0 || D > 3) return SPLAT_ERR_SIZE;
     if (P == 0) return SPLAT_OK;
     if (!geom || !binning || !image || !background || !means3D || !radii || !viewmatrix || !projmatrix ||
-        !projmatrix_raw || !dL_dout_color || !dL_dout_depth || !grad_scratch || !dL_dmeans2D || !dL_dcolors ||
-        !dL_dopacity || !dL_dmeans3D || !dL_dcov3D || !dL_dtau_partial)
+        !projmatrix_raw || !dL_dout_color || !dL_dout_depth || !grad_scratch || !dL_dtau_partial)
         return SPLAT_ERR_ARG;
-    if (shs && (!dL_dsh || !campos)) return SPLAT_ERR_ARG;
-    if (scales && (!rotations || !dL_dscales || !dL_drotations)) return SPLAT_ERR_ARG;
+    if (shs && !campos) return SPLAT_ERR_ARG;
+    if (shs && D > 0 && !dL_dsh) return SPLAT_ERR_ARG;        // the SH direction term also feeds the pose gradient
+    if (scales && (!rotations || ((dL_dscales == nullptr) != (dL_drotations == nullptr)))) return SPLAT_ERR_ARG;
     cudaStream_t s = (cudaStream_t)stream;
     const int gx = grid_dim(W), gy = grid_dim(H);
     GeomState g = GeomState::carve(geom, (size_t)P, nullptr);

@@ -209,7 +209,7 @@ preprocess_backward_kernel(BwdParams p, GeomState g, float* __restrict__ tau_par
             tau[2] += gd; tau[3] += gd * p_C.y; tau[4] += -gd * p_C.x;
 
             // ---------------- SH (backward.cu:532-534) ----------------
-            if (p.shs != nullptr) {
+            if (p.shs != nullptr && p.dL_dsh != nullptr) {
                 const f3 dm = sh_backward(p.D, p.M, p.shs + (size_t)idx * p.M * 3, m,
                                           mk(p.campos[0], p.campos[1], p.campos[2]), g.clamped[idx],
                                           mk(acc1.z, acc1.w, acc2.x), p.dL_dsh + (size_t)idx * p.M * 3);
@@ -217,7 +217,7 @@ preprocess_backward_kernel(BwdParams p, GeomState g, float* __restrict__ tau_par
                 tau[0] -= dm.x; tau[1] -= dm.y; tau[2] -= dm.z;
             }
             // ---------------- cov3D -> scale / rotation (backward.cu:350-413) ----------------
-            if (p.scales != nullptr) {
+            if (p.scales != nullptr && p.dL_dscale != nullptr) {
                 const float4 q4 = reinterpret_cast<const float4*>(p.rotations)[idx];
                 const float r = q4.x, x = q4.y, y = q4.z, z = q4.w;
                 // rows of Rq; glm's R has them as columns, M = S * R  ->  M(col c) = s (.) Rq-row c
@@ -251,19 +251,28 @@ preprocess_backward_kernel(BwdParams p, GeomState g, float* __restrict__ tau_par
                 reinterpret_cast<float4*>(p.dL_drot)[idx] = dq;
             }
         } else {
-            if (p.shs != nullptr)
+            if (p.shs != nullptr && p.dL_dsh != nullptr)
                 for (int k = 0; k < p.M * 3; ++k) p.dL_dsh[(size_t)idx * p.M * 3 + k] = 0.0f;
-            if (p.scales != nullptr) {
+            if (p.scales != nullptr && p.dL_dscale != nullptr) {
                 p.dL_dscale[3 * idx] = 0.0f; p.dL_dscale[3 * idx + 1] = 0.0f; p.dL_dscale[3 * idx + 2] = 0.0f;
                 reinterpret_cast<float4*>(p.dL_drot)[idx] = make_float4(0, 0, 0, 0);
             }
         }
-        p.dL_dmean2D[3 * idx] = acc0.x; p.dL_dmean2D[3 * idx + 1] = acc0.y; p.dL_dmean2D[3 * idx + 2] = 0.0f;
-        p.dL_dopacity[idx] = acc1.y;
-        p.dL_dcolors[3 * idx] = acc1.z; p.dL_dcolors[3 * idx + 1] = acc1.w; p.dL_dcolors[3 * idx + 2] = acc2.x;
-        p.dL_dmean3D[3 * idx] = dmean.x; p.dL_dmean3D[3 * idx + 1] = dmean.y; p.dL_dmean3D[3 * idx + 2] = dmean.z;
+        // outputs the caller does not want (NULL) are skipped: a pose-only tracking step needs none of them
+        if (p.dL_dmean2D) {
+            p.dL_dmean2D[3 * idx] = acc0.x; p.dL_dmean2D[3 * idx + 1] = acc0.y; p.dL_dmean2D[3 * idx + 2] = 0.0f;
+        }
+        if (p.dL_dopacity) p.dL_dopacity[idx] = acc1.y;
+        if (p.dL_dcolors) {
+            p.dL_dcolors[3 * idx] = acc1.z; p.dL_dcolors[3 * idx + 1] = acc1.w; p.dL_dcolors[3 * idx + 2] = acc2.x;
+        }
+        if (p.dL_dmean3D) {
+            p.dL_dmean3D[3 * idx] = dmean.x; p.dL_dmean3D[3 * idx + 1] = dmean.y; p.dL_dmean3D[3 * idx + 2] = dmean.z;
+        }
+        if (p.dL_dcov3D) {
 #pragma unroll
-        for (int k = 0; k < 6; ++k) p.dL_dcov3D[6 * (size_t)idx + k] = dcov[k];
+            for (int k = 0; k < 6; ++k) p.dL_dcov3D[6 * (size_t)idx + k] = dcov[k];
+        }
     }
     // camera-pose gradient: block-reduce the six components, one partial row per block
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;

@@ -127,11 +127,18 @@ def _forward_impl(S, means3D, sh, colors_precomp, opacities, scales, rotations, 
     return rendered, out_color, radii, geom, binning, image, out_depth, out_opacity, n_touched
 
 
+ALL_GRADS = dict(means2D=True, colors=True, opacity=True, means3D=True, cov3D=True, sh=True, scale_rot=True)
+
+
 def _backward_impl(S, means3D, radii, colors_precomp, scales, rotations, cov3Ds_precomp, grad_out_color, grad_out_depth,
-                   sh, geom, num_rendered, binning, image):
+                   sh, geom, num_rendered, binning, image, needs=None):
     """Equivalent of `_C.rasterize_gaussians_backward` (DGR/rasterize_points.cu:124-211) followed by the pose
     reduction of DGR __init__.py:152-154. Returns (dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D,
-    dL_dsh, dL_dscales, dL_drotations, grad_tau[6])."""
+    dL_dsh, dL_dscales, dL_drotations, grad_tau[6]).
+
+    `needs` (keys of ALL_GRADS) says which per-Gaussian gradients the caller wants; the others are neither allocated
+    nor computed and come back as None (e.g. pose-only tracking needs none of them). The reference always computes
+    everything."""
     L = _cabi.lib()
     dev = means3D.device
     P = means3D.size(0)
@@ -140,15 +147,21 @@ def _backward_impl(S, means3D, radii, colors_precomp, scales, rotations, cov3Ds_
     f32 = dict(dtype=torch.float32, device=dev)
     with torch.cuda.device(dev):
         stream = _cabi.stream_ptr(dev)
-        dL_dmeans3D = torch.empty((P, 3), **f32)
-        dL_dmeans2D = torch.empty((P, 3), **f32)
-        dL_dcolors = torch.empty((P, 3), **f32)
-        dL_dopacity = torch.empty((P, 1), **f32)
-        dL_dcov3D = torch.empty((P, 6), **f32)
-        dL_dsh = torch.empty((P, M, 3), **f32)
+        needs = ALL_GRADS if needs is None else needs
         has_scale = scales.numel() != 0
-        dL_dscales = torch.empty((P, 3), **f32) if has_scale else torch.zeros((P, 3), **f32)
-        dL_drotations = torch.empty((P, 4), **f32) if has_scale else torch.zeros((P, 4), **f32)
+        # the SH direction term also feeds the pose gradient, so dL_dsh is always computed when degree > 0
+        want_sh = M > 0 and (needs["sh"] or int(S.sh_degree) > 0)
+        dL_dmeans3D = torch.empty((P, 3), **f32) if needs["means3D"] else None
+        dL_dmeans2D = torch.empty((P, 3), **f32) if needs["means2D"] else None
+        dL_dcolors = torch.empty((P, 3), **f32) if needs["colors"] else None
+        dL_dopacity = torch.empty((P, 1), **f32) if needs["opacity"] else None
+        dL_dcov3D = torch.empty((P, 6), **f32) if needs["cov3D"] else None
+        dL_dsh = torch.empty((P, M, 3), **f32) if want_sh else None
+        if needs["scale_rot"]:
+            dL_dscales = torch.empty((P, 3), **f32) if has_scale else torch.zeros((P, 3), **f32)
+            dL_drotations = torch.empty((P, 4), **f32) if has_scale else torch.zeros((P, 4), **f32)
+        else:
+            dL_dscales = dL_drotations = None
         nblk = (P + 255) // 256
         tau_partial = torch.empty((nblk, 6), **f32)
         scratch = torch.empty((P * 12,), **f32)
@@ -164,9 +177,10 @@ def _backward_impl(S, means3D, radii, colors_precomp, scales, rotations, cov3Ds_
                 _cabi.ptr(_cabi.require_cuda("projmatrix_raw", S.projmatrix_raw)),
                 _cabi.ptr(_cabi.require_cuda("campos", S.campos)), float(S.tanfovx), float(S.tanfovy),
                 radii.data_ptr(), geom.data_ptr(), binning.data_ptr(), image.data_ptr(), gc.data_ptr(), gd.data_ptr(),
-                scratch.data_ptr(), dL_dmeans2D.data_ptr(), dL_dcolors.data_ptr(), dL_dopacity.data_ptr(),
-                dL_dmeans3D.data_ptr(), dL_dcov3D.data_ptr(), _cabi.ptr(dL_dsh), dL_dscales.data_ptr(),
-                dL_drotations.data_ptr(), tau_partial.data_ptr(), stream), "backward")
+                scratch.data_ptr(), _cabi.ptr(dL_dmeans2D), _cabi.ptr(dL_dcolors), _cabi.ptr(dL_dopacity),
+                _cabi.ptr(dL_dmeans3D), _cabi.ptr(dL_dcov3D), _cabi.ptr(dL_dsh),
+                _cabi.ptr(dL_dscales) if has_scale else None, _cabi.ptr(dL_drotations) if has_scale else None,
+                tau_partial.data_ptr(), stream), "backward")
             grad_tau = tau_partial.sum(dim=0)
         else:
             grad_tau = torch.zeros(6, **f32)
@@ -211,8 +225,12 @@ class _RasterizeGaussians(torch.autograd.Function):
             grad_out_color = torch.zeros((3, H, W), dtype=torch.float32, device=dev)
         if grad_out_depth is None:
             grad_out_depth = torch.zeros((1, H, W), dtype=torch.float32, device=dev)
+        # input order: means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp, theta, rho
+        ng = ctx.needs_input_grad
+        needs = dict(means3D=ng[0], means2D=ng[1], sh=ng[2], colors=ng[3], opacity=ng[4],
+                     scale_rot=ng[5] or ng[6], cov3D=ng[7])
         args = (S, _cabi.require_cuda("means3D", means3D), radii, colors_precomp, scales, rotations, cov3Ds_precomp,
-                grad_out_color, grad_out_depth, sh, geomBuffer, ctx.num_rendered, binningBuffer, imgBuffer)
+                grad_out_color, grad_out_depth, sh, geomBuffer, ctx.num_rendered, binningBuffer, imgBuffer, needs)
         if S.debug:
             cpu_args = cpu_deep_copy_tuple(args[1:])
             try:
@@ -227,6 +245,8 @@ class _RasterizeGaussians(torch.autograd.Function):
          grad_rotations, grad_tau) = res
         grad_rho = grad_tau[:3].view(1, -1)
         grad_theta = grad_tau[3:].view(1, -1)
+        if not ng[2]:
+            grad_sh = None          # computed only for its pose term
         grads = (grad_means3D, grad_means2D, grad_sh, grad_colors_precomp, grad_opacities, grad_scales, grad_rotations,
                  grad_cov3Ds_precomp, grad_theta, grad_rho, None)
         return grads
