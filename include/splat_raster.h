@@ -129,6 +129,23 @@ int splat_raster_backward_noalloc(
 int splat_raster_mark_visible(int P, const float* means3D, const float* viewmatrix, const float* projmatrix,
                               unsigned char* present, void* stream);
 
+/* Fused mapping loss, forward + backward in one pass (the step after the rasterizer on every view).
+ * Replaces get_loss_mapping / get_loss_mapping_rgbd with ssim_loss = False
+ * (thirdparty/monogs/utils/slam_utils.py:71-105):
+ *   loss = alpha * mean|(exp(a)*image + b)*m_rgb - gt_image*m_rgb| + (1-alpha) * mean|depth*m_d - gt_depth*m_d|,
+ *   m_rgb = gt_image.sum(0) > rgb_boundary_threshold, m_d = gt_depth > 0.01; `initialization` skips the exposure map.
+ * image/gt_image/dL_dimage are [3*H*W], depth/gt_depth/dL_ddepth [H*W], exposure_a/b one device float each.
+ * workspace: 4 + 4 * splat_raster_mapping_loss_blocks(W,H) floats, 16-byte aligned; its first 32-bit word is a ticket
+ *   counter that must be 0 on entry and is 0 again when the call has finished (zero it once, then reuse it for calls
+ *   that are ordered on one stream; concurrent streams need one workspace each).
+ * out: 5 floats = (loss, sum l1_rgb, sum l1_depth, dL/da, dL/db), summed in a fixed order (run-to-run deterministic).
+ * Gradients are for dL/dloss = 1. */
+int splat_raster_mapping_loss_blocks(int W, int H);
+int splat_raster_mapping_loss(int W, int H, const float* image, const float* depth, const float* gt_image,
+                              const float* gt_depth, const float* exposure_a, const float* exposure_b, float alpha,
+                              float rgb_boundary_threshold, int initialization, float* workspace, float* out,
+                              float* dL_dimage, float* dL_ddepth, void* stream);
+
 /* Test/diagnostic view into the opaque buffers (device pointers into the caller's buffers; layout is private).
  * Mirrors what the parity harness carves out of the reference's buffers (rasterizer_impl.cu:155-194). */
 typedef struct splat_raster_views {

@@ -230,6 +230,27 @@ int splat_raster_mark_visible(int P, const float* means3D, const float* viewmatr
     return SPLAT_OK;
 }
 
+int splat_raster_mapping_loss_blocks(int W, int H) {
+    if (W <= 0 || H <= 0) return 0;
+    return mapping_loss_blocks(W * H);
+}
+
+int splat_raster_mapping_loss(int W, int H, const float* image, const float* depth, const float* gt_image,
+                              const float* gt_depth, const float* exposure_a, const float* exposure_b, float alpha,
+                              float rgb_boundary_threshold, int initialization, float* workspace, float* out,
+                              float* dL_dimage, float* dL_ddepth, void* stream) {
+    if (W <= 0 || H <= 0) return SPLAT_ERR_SIZE;
+    if (!image || !depth || !gt_image || !gt_depth || !workspace || !out || !dL_dimage || !dL_ddepth)
+        return SPLAT_ERR_ARG;
+    if ((reinterpret_cast<uintptr_t>(workspace) & 15u) != 0) return SPLAT_ERR_ARG;
+    if (!initialization && (!exposure_a || !exposure_b)) return SPLAT_ERR_ARG;
+    launch_mapping_loss(W * H, image, depth, gt_image, gt_depth, exposure_a, exposure_b, alpha, rgb_boundary_threshold,
+                        initialization, workspace, out, dL_dimage, dL_ddepth, (cudaStream_t)stream);
+    g_launches += 1;
+    SPLAT_CUDA_CHECK_LAUNCH();
+    return SPLAT_OK;
+}
+
 int splat_raster_debug_views(int P, int R, int W, int H, void* geom, void* binning, void* image,
                              splat_raster_views* out) {
     if (!out || P < 0 || R < 0 || W <= 0 || H <= 0) return SPLAT_ERR_ARG;

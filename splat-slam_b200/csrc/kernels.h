@@ -41,6 +41,12 @@ void launch_ranges_and_records(int R, int tiles, const GeomState& g, const Binni
 int tile_sort_passes(int grid_x, int grid_y);
 void launch_sort_pairs(uint32_t* k0, uint32_t* v0, uint32_t* k1, uint32_t* v1, int n, int passes, uint32_t* scratch,
                        cudaStream_t s);
+// mapping_loss.cu
+int mapping_loss_blocks(int N);
+void launch_mapping_loss(int N, const float* image, const float* depth, const float* gt_image, const float* gt_depth,
+                         const float* exposure_a, const float* exposure_b, float alpha, float rgb_boundary_threshold,
+                         int initialization, float* workspace, float* out, float* dL_dimage, float* dL_ddepth,
+                         cudaStream_t s);
 // render.cu
 void launch_render_forward(int W, int H, int grid_x, int grid_y, const uint2* ranges, const float* records,
                            const float* bg, float* final_T, uint32_t* n_contrib, float* out_color, float* out_depth,

@@ -1,0 +1,113 @@
+"""Fused mapping loss (forward + backward in one CUDA pass) for the views a mapping step renders.
+
+Mirrors `get_loss_mapping(config, image, depth, viewpoint, opacity, initialization=False)` of the reference
+(thirdparty/monogs/utils/slam_utils.py:71-105, the `ssim_loss: False` path that configs/splat_slam.yaml:36 selects):
+same arguments, same value, same gradients w.r.t. `image`, `depth`, `viewpoint.exposure_a`, `viewpoint.exposure_b`,
+but one kernel instead of ~10 elementwise/reduction kernels, and the ground-truth depth is uploaded once per
+viewpoint instead of on every call (the reference does `torch.from_numpy(viewpoint.depth).to(device)` each time,
+slam_utils.py:87-89). No CPU path.
+"""
+from __future__ import annotations
+
+import ctypes
+from ctypes import c_float, c_int, c_void_p
+
+import torch
+
+from . import _cabi
+
+_fn = None
+_workspaces = {}       # (device index, stream handle) -> zeroed ticket + per-block partials, reused call after call
+
+
+def _entry():
+    global _fn
+    if _fn is None:
+        L = _cabi.lib()
+        f = L.splat_raster_mapping_loss
+        P = c_void_p
+        f.restype = c_int
+        f.argtypes = [c_int, c_int, P, P, P, P, P, P, c_float, c_float, c_int, P, P, P, P, P]
+        L.splat_raster_mapping_loss_blocks.restype = c_int
+        L.splat_raster_mapping_loss_blocks.argtypes = [c_int, c_int]
+        _fn = (f, L.splat_raster_mapping_loss_blocks)
+    return _fn
+
+
+class _FusedMappingLoss(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, image, depth, exposure_a, exposure_b, gt_image, gt_depth, alpha, rgb_boundary_threshold,
+                initialization):
+        fn, nblocks = _entry()
+        image = _cabi.require_cuda("image", image)
+        depth = _cabi.require_cuda("depth", depth)
+        gt_image = _cabi.require_cuda("gt_image", gt_image)
+        gt_depth = _cabi.require_cuda("gt_depth", gt_depth)
+        if image.dim() != 3 or image.size(0) != 3:
+            raise RuntimeError("image must have shape (3, H, W)")
+        H, W = image.size(1), image.size(2)
+        if depth.numel() != H * W or gt_depth.numel() != H * W or gt_image.shape != image.shape:
+            raise RuntimeError("depth / gt_image / gt_depth do not match the image shape")
+        dev = image.device
+        ea = eb = None
+        if not initialization:
+            ea = _cabi.require_cuda("exposure_a", exposure_a.reshape(-1))
+            eb = _cabi.require_cuda("exposure_b", exposure_b.reshape(-1))
+        with torch.cuda.device(dev):
+            stream = _cabi.stream_ptr(dev)
+            words = 4 + 4 * nblocks(W, H)
+            ws = _workspaces.get((dev.index, stream))
+            if ws is None or ws.numel() < words:
+                # zeroed once; the kernel hands the ticket word back as 0, and calls on one stream are ordered
+                ws = _workspaces[(dev.index, stream)] = torch.zeros(words, dtype=torch.float32, device=dev)
+            out = torch.empty(5, dtype=torch.float32, device=dev)
+            dimg = torch.empty_like(image)
+            ddepth = torch.empty_like(depth)
+            _cabi.check(fn(W, H, image.data_ptr(), depth.data_ptr(), gt_image.data_ptr(), gt_depth.data_ptr(),
+                           _cabi.ptr(ea), _cabi.ptr(eb), float(alpha), float(rgb_boundary_threshold),
+                           int(bool(initialization)), ws.data_ptr(), out.data_ptr(), dimg.data_ptr(),
+                           ddepth.data_ptr(), stream), "mapping_loss")
+            loss = out[0]
+        ctx.save_for_backward(dimg, ddepth, out)
+        ctx.initialization = bool(initialization)
+        ctx.exposure_shapes = (None if exposure_a is None else exposure_a.shape,
+                               None if exposure_b is None else exposure_b.shape)
+        return loss
+
+    @staticmethod
+    def backward(ctx, grad_loss):
+        dimg, ddepth, sums = ctx.saved_tensors
+        ga = gb = None
+        if not ctx.initialization:
+            ga = (grad_loss * sums[3]).reshape(ctx.exposure_shapes[0])
+            gb = (grad_loss * sums[4]).reshape(ctx.exposure_shapes[1])
+        return grad_loss * dimg, grad_loss * ddepth, ga, gb, None, None, None, None, None
+
+
+def fused_mapping_loss(image, depth, exposure_a, exposure_b, gt_image, gt_depth, alpha=0.95,
+                       rgb_boundary_threshold=0.01, initialization=False):
+    """loss = alpha * mean|image_ab*m - gt_image*m| + (1-alpha) * mean|depth*md - gt_depth*md| (see module docstring)."""
+    return _FusedMappingLoss.apply(image, depth, exposure_a, exposure_b, gt_image, gt_depth, alpha,
+                                   rgb_boundary_threshold, initialization)
+
+
+def get_loss_mapping(config, image, depth, viewpoint, opacity, initialization=False):
+    """Drop-in for thirdparty/monogs/utils/slam_utils.py:71-78 (+ get_loss_mapping_rgbd :81-105)."""
+    training = config["Training"]
+    if training.get("ssim_loss", False):
+        raise NotImplementedError("fused mapping loss covers the ssim_loss: False path only (configs/splat_slam.yaml:36)")
+    alpha = training["alpha"] if "alpha" in training else 0.95
+    thr = training["rgb_boundary_threshold"]
+    gt_image = viewpoint.original_image
+    if not gt_image.is_cuda:
+        gt_image = gt_image.cuda()
+    gt_depth = getattr(viewpoint, "_depth_cuda", None)
+    if gt_depth is None or gt_depth.device != image.device:
+        d = viewpoint.depth
+        gt_depth = (torch.from_numpy(d) if not torch.is_tensor(d) else d).to(dtype=torch.float32, device=image.device)[None]
+        try:
+            viewpoint._depth_cuda = gt_depth      # uploaded once per viewpoint, not once per call
+        except Exception:
+            pass
+    return fused_mapping_loss(image, depth, viewpoint.exposure_a, viewpoint.exposure_b, gt_image, gt_depth, alpha, thr,
+                              initialization)
