@@ -146,6 +146,25 @@ int splat_raster_mapping_loss(int W, int H, const float* image, const float* dep
                               float rgb_boundary_threshold, int initialization, float* workspace, float* out,
                               float* dL_dimage, float* dL_ddepth, void* stream);
 
+/* Fused Adam step over a list of tensors in one launch per 32 tensors (the step after backward).
+ * Replaces `self.gaussians.optimizer.step()` / `self.keyframe_optimizers.step()` (src/mapper.py:557-562), i.e.
+ * torch.optim.Adam as configured in thirdparty/gaussian_splatting/scene/gaussian_model.py:264-302 (one lr per group,
+ * eps = 1e-15, betas 0.9/0.999, no weight decay, no amsgrad) and src/mapper.py:1111:
+ *   m = lerp(m, g, 1-beta1); v = v*beta2 + (1-beta2)*g*g; p -= lr/(1-beta1^step) * m / (sqrt(v)/sqrt(1-beta2^step) + eps)
+ * `step` is the 1-based count of this update. All pointers are device float arrays of n elements; `segments` itself is
+ * a HOST array. zero_grads != 0 also clears each grad (for callers that accumulate into a persistent buffer instead
+ * of `zero_grad(set_to_none=True)`). */
+typedef struct splat_raster_adam_segment {
+    float* param;
+    float* grad;
+    float* exp_avg;
+    float* exp_avg_sq;
+    long long n;
+    double lr, beta1, beta2, eps;
+    long long step;
+} splat_raster_adam_segment;
+int splat_raster_adam_step(int num_segments, const splat_raster_adam_segment* segments, int zero_grads, void* stream);
+
 /* Test/diagnostic view into the opaque buffers (device pointers into the caller's buffers; layout is private).
  * Mirrors what the parity harness carves out of the reference's buffers (rasterizer_impl.cu:155-194). */
 typedef struct splat_raster_views {

@@ -3,6 +3,9 @@
 #include "common.cuh"
 #include "kernels.h"
 
+#include <cmath>
+#include <vector>
+
 using namespace splat;
 
 namespace {
@@ -247,6 +250,35 @@ int splat_raster_mapping_loss(int W, int H, const float* image, const float* dep
     launch_mapping_loss(W * H, image, depth, gt_image, gt_depth, exposure_a, exposure_b, alpha, rgb_boundary_threshold,
                         initialization, workspace, out, dL_dimage, dL_ddepth, (cudaStream_t)stream);
     g_launches += 1;
+    SPLAT_CUDA_CHECK_LAUNCH();
+    return SPLAT_OK;
+}
+
+int splat_raster_adam_step(int num_segments, const splat_raster_adam_segment* segments, int zero_grads, void* stream) {
+    if (num_segments < 0 || (num_segments > 0 && !segments)) return SPLAT_ERR_ARG;
+    std::vector<AdamSegment> segs;
+    segs.reserve((size_t)num_segments);
+    for (int i = 0; i < num_segments; ++i) {
+        const splat_raster_adam_segment& in = segments[i];
+        if (in.n < 0 || in.step < 1) return SPLAT_ERR_ARG;
+        if (in.n == 0) continue;
+        if (!in.param || !in.grad || !in.exp_avg || !in.exp_avg_sq) return SPLAT_ERR_ARG;
+        // scalars in double, then narrowed, exactly as torch hands Python floats to its float kernels
+        const double bc1 = 1.0 - std::pow(in.beta1, (double)in.step);
+        const double bc2 = 1.0 - std::pow(in.beta2, (double)in.step);
+        AdamSegment s;
+        s.p = in.param; s.g = in.grad; s.m = in.exp_avg; s.v = in.exp_avg_sq; s.n = in.n;
+        s.w1 = (float)(1.0 - in.beta1);
+        s.beta2 = (float)in.beta2;
+        s.w2 = (float)(1.0 - in.beta2);
+        s.bc2_sqrt = (float)std::sqrt(bc2);
+        s.eps = (float)in.eps;
+        s.neg_step = (float)(-(in.lr / bc1));
+        s.vec4 = 0;
+        segs.push_back(s);
+    }
+    if (segs.empty()) return SPLAT_OK;
+    g_launches += launch_adam_step((int)segs.size(), segs.data(), zero_grads, (cudaStream_t)stream);
     SPLAT_CUDA_CHECK_LAUNCH();
     return SPLAT_OK;
 }

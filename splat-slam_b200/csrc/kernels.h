@@ -47,6 +47,15 @@ void launch_mapping_loss(int N, const float* image, const float* depth, const fl
                          const float* exposure_a, const float* exposure_b, float alpha, float rgb_boundary_threshold,
                          int initialization, float* workspace, float* out, float* dL_dimage, float* dL_ddepth,
                          cudaStream_t s);
+// adam.cu
+constexpr int kAdamMaxSegments = 32;      // tensors per launch (kernel-parameter space)
+struct AdamSegment {
+    float* p; float* g; float* m; float* v;
+    long long n;
+    float w1, beta2, w2, bc2_sqrt, eps, neg_step;
+    int vec4;
+};
+int launch_adam_step(int count, const AdamSegment* segments, int zero_grads, cudaStream_t stream);   // -> launches
 // render.cu
 void launch_render_forward(int W, int H, int grid_x, int grid_y, const uint2* ranges, const float* records,
                            const float* bg, float* final_T, uint32_t* n_contrib, float* out_color, float* out_depth,
