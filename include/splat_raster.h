@@ -165,6 +165,23 @@ typedef struct splat_raster_adam_segment {
 } splat_raster_adam_segment;
 int splat_raster_adam_step(int num_segments, const splat_raster_adam_segment* segments, int zero_grads, void* stream);
 
+/* Densification bookkeeping for the K views of one mapping iteration, one launch per 16 views.
+ * Replaces the per-view loop of src/mapper.py:519-529 + GaussianModel.add_densification_stats
+ * (thirdparty/gaussian_splatting/scene/gaussian_model.py:738-742): for every view k in order and every Gaussian with
+ * radii_k > 0:  max_radii2D = max(max_radii2D, radii_k);  xyz_gradient_accum += hypot of viewspace_grad_k[:2];
+ * denom += 1.  `radii` / `viewspace_grad` are HOST arrays of K device pointers ([P] int, [P*grad_stride] float with
+ * grad_stride >= 2, 3 for the rasterizer's dL_dmeans2D); the three statistics are [P] device floats updated in place. */
+int splat_raster_densify_stats(int P, int K, const int* const* radii, const float* const* viewspace_grad,
+                               int grad_stride, float* max_radii2D, float* xyz_gradient_accum, float* denom,
+                               void* stream);
+
+/* Occlusion-aware visibility of the window views (src/mapper.py:494-499,507-509): visibility[k][i] =
+ * n_touched[k][i] > 0 as int64 (the reference's `.long()`), n_obs[i] = number of views that touched Gaussian i.
+ * `n_touched` / `visibility` are HOST arrays of K device pointers; `visibility` (or single entries) and `n_obs` may
+ * be NULL. */
+int splat_raster_visibility_count(int P, int K, const int* const* n_touched, long long* const* visibility,
+                                  int* n_obs, void* stream);
+
 /* Test/diagnostic view into the opaque buffers (device pointers into the caller's buffers; layout is private).
  * Mirrors what the parity harness carves out of the reference's buffers (rasterizer_impl.cu:155-194). */
 typedef struct splat_raster_views {

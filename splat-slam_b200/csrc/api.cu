@@ -283,6 +283,32 @@ int splat_raster_adam_step(int num_segments, const splat_raster_adam_segment* se
     return SPLAT_OK;
 }
 
+int splat_raster_densify_stats(int P, int K, const int* const* radii, const float* const* viewspace_grad,
+                               int grad_stride, float* max_radii2D, float* xyz_gradient_accum, float* denom,
+                               void* stream) {
+    if (P < 0 || K < 0 || grad_stride < 2) return SPLAT_ERR_ARG;
+    if (P == 0 || K == 0) return SPLAT_OK;
+    if (!radii || !viewspace_grad || !max_radii2D || !xyz_gradient_accum || !denom) return SPLAT_ERR_ARG;
+    for (int k = 0; k < K; ++k)
+        if (!radii[k] || !viewspace_grad[k]) return SPLAT_ERR_ARG;
+    g_launches += launch_densify_stats(P, K, radii, viewspace_grad, grad_stride, max_radii2D, xyz_gradient_accum, denom,
+                                       (cudaStream_t)stream);
+    SPLAT_CUDA_CHECK_LAUNCH();
+    return SPLAT_OK;
+}
+
+int splat_raster_visibility_count(int P, int K, const int* const* n_touched, long long* const* visibility,
+                                  int* n_obs, void* stream) {
+    if (P < 0 || K < 0) return SPLAT_ERR_ARG;
+    if (P == 0 || K == 0) return SPLAT_OK;
+    if (!n_touched) return SPLAT_ERR_ARG;
+    for (int k = 0; k < K; ++k)
+        if (!n_touched[k]) return SPLAT_ERR_ARG;
+    g_launches += launch_visibility_count(P, K, n_touched, visibility, n_obs, (cudaStream_t)stream);
+    SPLAT_CUDA_CHECK_LAUNCH();
+    return SPLAT_OK;
+}
+
 int splat_raster_debug_views(int P, int R, int W, int H, void* geom, void* binning, void* image,
                              splat_raster_views* out) {
     if (!out || P < 0 || R < 0 || W <= 0 || H <= 0) return SPLAT_ERR_ARG;

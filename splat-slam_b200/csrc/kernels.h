@@ -56,6 +56,12 @@ struct AdamSegment {
     int vec4;
 };
 int launch_adam_step(int count, const AdamSegment* segments, int zero_grads, cudaStream_t stream);   // -> launches
+// densify.cu
+constexpr int kDensifyMaxViews = 16;      // views per launch (kernel-parameter space)
+int launch_densify_stats(int P, int K, const int* const* radii, const float* const* grad, int grad_stride,
+                         float* max_radii2D, float* xyz_gradient_accum, float* denom, cudaStream_t s);   // -> launches
+int launch_visibility_count(int P, int K, const int* const* n_touched, long long* const* visibility, int* n_obs,
+                            cudaStream_t s);                                                             // -> launches
 // render.cu
 void launch_render_forward(int W, int H, int grid_x, int grid_y, const uint2* ranges, const float* records,
                            const float* bg, float* final_T, uint32_t* n_contrib, float* out_color, float* out_depth,

@@ -34,6 +34,7 @@ EXPORTS = (
     "splat_raster_mark_visible", "splat_raster_debug_views", "splat_raster_launch_count", "splat_raster_profile",
     "splat_raster_stage_count", "splat_raster_stage_name", "splat_raster_profile_read",
     "splat_raster_mapping_loss_blocks", "splat_raster_mapping_loss", "splat_raster_adam_step",
+    "splat_raster_densify_stats", "splat_raster_visibility_count",
 )
 
 
