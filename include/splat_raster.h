@@ -182,6 +182,15 @@ int splat_raster_densify_stats(int P, int K, const int* const* radii, const floa
 int splat_raster_visibility_count(int P, int K, const int* const* n_touched, long long* const* visibility,
                                   int* n_obs, void* stream);
 
+/* mean_dist2[i] = mean of the squared distances from point i to its three nearest neighbours.
+ * Replaces simple_knn._C.distCUDA2 (thirdparty/simple-knn/spatial.cu:15-26 -> SimpleKNN::knn, simple_knn.cu:174-216),
+ * which gaussian_model.py:194-200 calls at every keyframe insert. points is [P*3] device floats, mean_dist2 [P];
+ * scratch is splat_raster_knn_scratch_bytes(P) bytes of device memory with no state between calls. Like the
+ * reference, fewer than four points leave unfilled neighbour slots at FLT_MAX (the mean overflows to +inf), and
+ * coincident points count with distance 0. No host synchronisation. */
+size_t splat_raster_knn_scratch_bytes(int P);
+int splat_raster_knn_mean_dist2(int P, const float* points, void* scratch, float* mean_dist2, void* stream);
+
 /* Test/diagnostic view into the opaque buffers (device pointers into the caller's buffers; layout is private).
  * Mirrors what the parity harness carves out of the reference's buffers (rasterizer_impl.cu:155-194). */
 typedef struct splat_raster_views {

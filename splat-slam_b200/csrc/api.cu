@@ -309,6 +309,18 @@ int splat_raster_visibility_count(int P, int K, const int* const* n_touched, lon
     return SPLAT_OK;
 }
 
+size_t splat_raster_knn_scratch_bytes(int P) { return P > 0 ? knn_scratch_bytes((size_t)P) : 256; }
+
+int splat_raster_knn_mean_dist2(int P, const float* points, void* scratch, float* mean_dist2, void* stream) {
+    if (P < 0) return SPLAT_ERR_SIZE;
+    if (P == 0) return SPLAT_OK;
+    if (!points || !scratch || !mean_dist2) return SPLAT_ERR_ARG;
+    if ((reinterpret_cast<uintptr_t>(scratch) & 255u) != 0) return SPLAT_ERR_ARG;
+    g_launches += launch_knn_mean_dist2(P, points, scratch, mean_dist2, (cudaStream_t)stream);
+    SPLAT_CUDA_CHECK_LAUNCH();
+    return SPLAT_OK;
+}
+
 int splat_raster_debug_views(int P, int R, int W, int H, void* geom, void* binning, void* image,
                              splat_raster_views* out) {
     if (!out || P < 0 || R < 0 || W <= 0 || H <= 0) return SPLAT_ERR_ARG;

@@ -62,6 +62,9 @@ int launch_densify_stats(int P, int K, const int* const* radii, const float* con
                          float* max_radii2D, float* xyz_gradient_accum, float* denom, cudaStream_t s);   // -> launches
 int launch_visibility_count(int P, int K, const int* const* n_touched, long long* const* visibility, int* n_obs,
                             cudaStream_t s);                                                             // -> launches
+// knn.cu
+size_t knn_scratch_bytes(size_t P);
+int launch_knn_mean_dist2(int P, const float* points, void* scratch, float* mean_dist2, cudaStream_t s);   // -> launches
 // render.cu
 void launch_render_forward(int W, int H, int grid_x, int grid_y, const uint2* ranges, const float* records,
                            const float* bg, float* final_T, uint32_t* n_contrib, float* out_color, float* out_depth,

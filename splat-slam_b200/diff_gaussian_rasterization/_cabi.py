@@ -35,6 +35,7 @@ EXPORTS = (
     "splat_raster_stage_count", "splat_raster_stage_name", "splat_raster_profile_read",
     "splat_raster_mapping_loss_blocks", "splat_raster_mapping_loss", "splat_raster_adam_step",
     "splat_raster_densify_stats", "splat_raster_visibility_count",
+    "splat_raster_knn_scratch_bytes", "splat_raster_knn_mean_dist2",
 )
 
 
