@@ -12,8 +12,9 @@ import torch
 
 import parity as T
 
-GOLDEN = sorted(p for p in glob.glob(os.path.join(os.path.dirname(__file__), "golden", "*.pt"))
-                if os.path.basename(p) not in ("mapping_loss.pt", "densify_stats.pt"))   # those have their own tests
+# rasterizer fixtures only (make_golden.py); mapping_loss / densify_stats / knn fixtures have their own tests
+GOLDEN = sorted(p for pat in ("tiny_*.pt", "ragged_*.pt")
+                for p in glob.glob(os.path.join(os.path.dirname(__file__), "golden", pat)))
 
 
 def case_from_fixture(fx):
