@@ -55,6 +55,9 @@ def parse():
     ap.add_argument("--views", type=int, default=VIEWS_PER_RANK)
     ap.add_argument("--camera", default=CAMERA)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--streams", type=int, default=3,
+                    help="views of a step are issued round-robin on this many CUDA streams (ours only; the reference "
+                         "extension launches on the legacy default stream and always runs with 1)")
     return ap.parse_args()
 
 
@@ -123,7 +126,7 @@ class Workload:
 
     def __init__(self, mod, args, device, rank, world):
         from diff_gaussian_rasterization import synthetic as syn
-        from diff_gaussian_rasterization.window import FlatGrads, partition_views
+        from diff_gaussian_rasterization.window import FlatGrads, ViewStreams, partition_views
         self.mod, self.device, self.syn = mod, device, syn
         g = syn.make_gaussians(args.camera, args.gaussians, seed=0, sh_coeffs=1)
         self.params = {k: g[k].to(device).requires_grad_(True) for k in ("means3D", "shs", "opacities", "scales", "rotations")}
@@ -149,11 +152,13 @@ class Workload:
         self.rho = [torch.zeros(3, device=device, requires_grad=True) for _ in self.view_ids]
         self.means2D = torch.zeros_like(self.params["means3D"], requires_grad=True)
         # e2e leg: double-buffered device staging filled by a copy stream, so the next view's H2D overlaps compute
-        self.stage_mats = [torch.empty_like(self.d_mats[0]) for _ in range(2)] if self.d_mats else None
-        self.stage_up = [torch.empty_like(self.d_up) for _ in range(2)]
+        self.streams = ViewStreams(device, args.streams if mod.__name__ == "diff_gaussian_rasterization" else 1)
+        self.nbuf = max(2, len(self.streams) + 1)      # one staging buffer per view in flight, plus the one being filled
+        self.stage_mats = [torch.empty_like(self.d_mats[0]) for _ in range(self.nbuf)] if self.d_mats else None
+        self.stage_up = [torch.empty_like(self.d_up) for _ in range(self.nbuf)]
         self.copy_stream = torch.cuda.Stream(device=device)
-        self.ev_ready = [torch.cuda.Event() for _ in range(2)]
-        self.ev_free = [torch.cuda.Event() for _ in range(2)]
+        self.ev_ready = [torch.cuda.Event() for _ in range(self.nbuf)]
+        self.ev_free = [torch.cuda.Event() for _ in range(self.nbuf)]
         self.last = {}
 
     def settings(self, i, mats):
@@ -175,8 +180,13 @@ class Workload:
 
     def step_resident(self):
         self.flat.zero_()
+        # views are independent until their gradients are accumulated: window.ViewStreams issues them round-robin on a
+        # few streams (one view's latency-bound sort passes hide under another view's render kernels)
+        self.streams.fork()
         for i in range(len(self.view_ids)):
-            self.render_backward(i, self.d_mats[i], self.d_up)
+            with self.streams.view(i):
+                self.render_backward(i, self.d_mats[i], self.d_up)
+        self.streams.join()
         self.flat.all_reduce()
 
     def step_e2e(self):
@@ -185,7 +195,7 @@ class Workload:
         n = len(self.view_ids)
 
         def prefetch(i):
-            b = i & 1
+            b = i % self.nbuf
             with torch.cuda.stream(self.copy_stream):
                 self.copy_stream.wait_event(self.ev_free[b])       # the view that used this buffer is done
                 self.stage_mats[b].copy_(self.h_mats[i], non_blocking=True)
@@ -193,21 +203,27 @@ class Workload:
                 self.ev_ready[b].record(self.copy_stream)
 
         self.flat.zero_()
-        acc = torch.zeros((), device=self.device)
-        for b in range(2):
+        lanes = max(1, len(self.streams))
+        acc = [torch.zeros((), device=self.device) for _ in range(lanes)]      # one running result per stream
+        for b in range(self.nbuf):
             self.ev_free[b].record(main)
+        self.streams.fork()
         if n:
             prefetch(0)
         for i in range(n):
-            b = i & 1
+            b = i % self.nbuf
             if i + 1 < n:
                 prefetch(i + 1)
-            main.wait_event(self.ev_ready[b])
-            color, depth = self.render_backward(i, self.stage_mats[b], self.stage_up[b])
-            acc = acc + (color.detach() * self.stage_up[b][:3]).sum() + (depth.detach() * self.stage_up[b][3:4]).sum()
-            self.ev_free[b].record(main)
+            with self.streams.view(i):
+                st = self.streams.stream(i)
+                st.wait_event(self.ev_ready[b])
+                color, depth = self.render_backward(i, self.stage_mats[b], self.stage_up[b])
+                acc[i % lanes] = (acc[i % lanes] + (color.detach() * self.stage_up[b][:3]).sum()
+                                  + (depth.detach() * self.stage_up[b][3:4]).sum())
+                self.ev_free[b].record(st)
+        self.streams.join()
         self.flat.all_reduce()
-        return float(acc.item())
+        return float(torch.stack(acc).sum().item())
 
     def h2d_bytes_per_step(self):
         return len(self.view_ids) * (self.h_mats[0].numel() * 4 + self.h_up.numel() * 4) if self.view_ids else 0
@@ -318,6 +334,7 @@ def main():
     ms_e2e = timed(wl.step_e2e, args.steps, max(1, args.warmup // 2), device, ref_world)
     clocks = sampler.stop() if sampler else None
 
+    n_streams = max(1, len(wl.streams))
     value = views_per_step_global * args.steps / (ms_value * 1e-3)
     e2e = views_per_step_global * args.steps / (ms_e2e * 1e-3)
 
@@ -330,6 +347,8 @@ def main():
     peak, peak_src = peaks()
     if kind == "ours":
         R = int(mod._PinnedInt.get(device).item())
+        from diff_gaussian_rasterization.window import ViewStreams
+        wl.streams = ViewStreams(device, 1)     # per-stage times are taken with the views back to back on one stream
         _cabi.profile(True)
         _cabi.profile_read(reset=True)
         for _ in range(2):
@@ -375,7 +394,8 @@ def main():
                        "collective": "all_reduce(sum,fp32) of the flat Gaussian-gradient buffer, "
                                      f"{wl.flat.flat.numel() * 4} B/step" if ref_world > 1 else "none (1 GPU)",
                        "l2": "inputs larger than L2: ~0.4 GB of state per view, 10 distinct views per step",
-                       "resident": "Gaussian parameters stay in HBM (model state)"},
+                       "resident": "Gaussian parameters stay in HBM (model state)",
+                       "streams": n_streams},
             "e2e": {"value": e2e, "unit": "it/s", "h2d_bytes_per_step": wl.h2d_bytes_per_step(),
                     "d2h_bytes_per_step": wl.d2h_bytes_per_step(), "ms_per_step": ms_e2e / args.steps},
             "gpu_launches": int(launches0) if kind == "ours" else 0,

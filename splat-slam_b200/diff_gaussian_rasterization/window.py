@@ -11,6 +11,7 @@ One process per GPU, `torch.distributed` (NCCL over NVLink on the GPU box, gloo 
 """
 from __future__ import annotations
 
+import contextlib
 from typing import Callable, Dict, List, Optional, Sequence
 
 import torch
@@ -58,21 +59,68 @@ class FlatGrads:
             dist.all_reduce(self.flat, op=dist.ReduceOp.SUM, group=group)
 
 
+class ViewStreams:
+    """Round-robin CUDA streams for the views of one window step.
+
+    The views are independent until autograd accumulates their gradients, so issuing them on a few streams lets one
+    view's latency-bound sort passes and its num_rendered hand-off (the one host sync of a forward) hide under another
+    view's render kernels. `fork()` makes the side streams wait for the work queued so far, `join()` makes the
+    caller's stream wait for all of them. With n <= 1 everything stays on the caller's stream."""
+
+    def __init__(self, device, n: int = 3):
+        self.device = torch.device(device)
+        self.streams = [torch.cuda.Stream(device=self.device) for _ in range(n)] if n > 1 else []
+        if self.streams:   # accumulation into the shared leaves deliberately crosses streams; autograd orders it
+            torch.autograd.graph.set_warn_on_accumulate_grad_stream_mismatch(False)
+
+    def __len__(self):
+        return len(self.streams)
+
+    def fork(self):
+        main = torch.cuda.current_stream(self.device) if self.streams else None
+        for st in self.streams:
+            st.wait_stream(main)
+
+    def view(self, i: int):
+        """Context manager: the stream view number i of the step runs on."""
+        if not self.streams:
+            return contextlib.nullcontext()
+        return torch.cuda.stream(self.streams[i % len(self.streams)])
+
+    def stream(self, i: int):
+        return self.streams[i % len(self.streams)] if self.streams else torch.cuda.current_stream(self.device)
+
+    def join(self):
+        main = torch.cuda.current_stream(self.device) if self.streams else None
+        for st in self.streams:
+            main.wait_stream(st)
+
+
 def window_step(render_view: Callable[[int], Sequence[torch.Tensor]],
                 upstream: Callable[[int], Sequence[torch.Tensor]],
-                flat: FlatGrads, n_views: int, group=None, views: Optional[List[int]] = None) -> List[int]:
+                flat: FlatGrads, n_views: int, group=None, views: Optional[List[int]] = None,
+                streams: Optional[ViewStreams] = None) -> List[int]:
     """One mapping iteration over a window of `n_views` views.
 
     render_view(v) -> tensors to differentiate (e.g. (color, depth)) for global view index v;
     upstream(v)    -> matching upstream gradients (dL/dcolor, dL/ddepth).
     Gradients of the Gaussian parameters accumulate in `flat`; after the local views are done they are
-    all-reduced over `group`. Returns the list of view indices this rank rendered."""
+    all-reduced over `group`. `streams` (CUDA only) spreads the local views over a few streams.
+    Returns the list of view indices this rank rendered."""
     world = dist.get_world_size(group) if (dist.is_available() and dist.is_initialized()) else 1
     rank = dist.get_rank(group) if world > 1 else 0
     mine = partition_views(n_views, world, rank) if views is None else views
     flat.zero_()
-    for v in mine:
-        outs = render_view(v)
-        torch.autograd.backward(list(outs), list(upstream(v)))
+    if streams is not None and len(streams):
+        streams.fork()
+        for k, v in enumerate(mine):
+            with streams.view(k):
+                outs = render_view(v)
+                torch.autograd.backward(list(outs), list(upstream(v)))
+        streams.join()
+    else:
+        for v in mine:
+            outs = render_view(v)
+            torch.autograd.backward(list(outs), list(upstream(v)))
     flat.all_reduce(group)
     return mine

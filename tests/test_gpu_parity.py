@@ -291,3 +291,42 @@ def test_linearity_in_upstream_gradient():
     b = T.run_module(m, case2)
     for k in ("means3D", "shs", "opacities", "scales", "rotations", "theta", "rho"):
         assert T.rel_err(b["grad_" + k], 2 * a["grad_" + k]) < 1e-4, k
+
+
+@pytest.mark.gpu
+def test_window_step_on_several_streams_matches_one_stream():
+    """window.ViewStreams issues the views of a step round-robin on side streams; the accumulated Gaussian gradients and
+    the per-view pose gradients must be those of the plain sequential loop (up to the backward's atomic-add order)."""
+    from diff_gaussian_rasterization import synthetic as syn
+    from diff_gaussian_rasterization.window import FlatGrads, ViewStreams, window_step
+    m = T.load_ours()
+    cam, P, n_views = "small", 20_000, 7
+    g = syn.make_gaussians(cam, P, seed=3, sh_coeffs=1)
+    Wc, Wd = (t.cuda() for t in syn.upstream_grads(cam))
+    res = []
+    for n_streams in (1, 3):
+        params = {k: g[k].cuda().requires_grad_(True) for k in ("means3D", "shs", "opacities", "scales", "rotations")}
+        flat = FlatGrads(params)
+        theta = [torch.zeros(3, device="cuda", requires_grad=True) for _ in range(n_views)]
+        rho = [torch.zeros(3, device="cuda", requires_grad=True) for _ in range(n_views)]
+        means2D = torch.zeros(P, 3, device="cuda", requires_grad=True)
+
+        def render_view(v):
+            view = syn.make_view(cam, syn.window_pose(v))
+            S = m.GaussianRasterizationSettings(
+                image_height=view.image_height, image_width=view.image_width, tanfovx=view.tanfovx, tanfovy=view.tanfovy,
+                bg=torch.zeros(3, device="cuda"), scale_modifier=1.0, viewmatrix=view.viewmatrix.cuda(),
+                projmatrix=view.projmatrix.cuda(), projmatrix_raw=view.projmatrix_raw.cuda(), sh_degree=0,
+                campos=view.campos.cuda(), prefiltered=False, debug=False)
+            color, radii, depth, opacity, n_touched = m.GaussianRasterizer(S)(
+                means3D=params["means3D"], means2D=means2D, opacities=params["opacities"], shs=params["shs"],
+                scales=params["scales"], rotations=params["rotations"], theta=theta[v], rho=rho[v])
+            return color, depth
+
+        for _ in range(2):          # second pass re-uses the cached allocator blocks across streams
+            window_step(render_view, lambda v: (Wc, Wd), flat, n_views, streams=ViewStreams("cuda:0", n_streams))
+            torch.cuda.synchronize()
+        res.append((flat.flat.clone(), torch.stack([t.grad for t in theta]), torch.stack([r.grad for r in rho]),
+                    means2D.grad.clone()))
+    for a, b in zip(res[1], res[0]):
+        assert T.rel_err(a, b) <= 1e-4
