@@ -191,6 +191,30 @@ int splat_raster_visibility_count(int P, int K, const int* const* n_touched, lon
 size_t splat_raster_knn_scratch_bytes(int P);
 int splat_raster_knn_mean_dist2(int P, const float* points, void* scratch, float* mean_dist2, void* stream);
 
+/* Map deformation: move the Gaussians anchored to updated keyframes with their keyframe.
+ * Replaces Mapper.update_mapping_points (src/mapper.py:154-255), for any number of keyframes at once:
+ *   rigid != 0 : mean' = T [mean,1] with T = inv(inv(w2c_old) @ w2c_new); rot' = quat(T) (x) normalize(rot)
+ *   rigid == 0 : additionally rescale the point along its old camera ray by s = 1 + (depth_new - depth_old) / z_cam at
+ *                the pixel it projects to (clamped to the image; s = 1 where a depth is 0 or s <= 0) before moving
+ *                it, and add log(s) to its three log-scales.
+ * Every Gaussian's rotation is written back normalised, as the reference does (mapper.py:176,245).
+ * keyframes is a HOST array; its matrices are DEVICE pointers to 16 row-major floats, depth maps DEVICE [H*W] floats
+ * (unused when rigid). kf_ids [P] is the device copy of GaussianModel.unique_kfIDs (int32), intrinsics 9 device
+ * floats (may be NULL when every keyframe is rigid). table: SPLAT_DEFORM_TABLE_FLOATS device floats of scratch.
+ * xyz [P*3], rotation [P*4] (16-byte aligned), scaling [P*3] are updated in place. No host synchronisation. */
+#define SPLAT_DEFORM_TABLE_FLOATS 2560
+typedef struct splat_raster_deform_keyframe {
+    const float* w2c_old;
+    const float* w2c_new;
+    const float* depth_new;
+    const float* depth_old;
+    int frame_idx;
+    int rigid;
+} splat_raster_deform_keyframe;
+int splat_raster_deform_points(int P, int K, const splat_raster_deform_keyframe* keyframes, const int* kf_ids,
+                               const float* intrinsics, int W, int H, float* table, float* xyz, float* rotation,
+                               float* scaling, void* stream);
+
 /* Test/diagnostic view into the opaque buffers (device pointers into the caller's buffers; layout is private).
  * Mirrors what the parity harness carves out of the reference's buffers (rasterizer_impl.cu:155-194). */
 typedef struct splat_raster_views {

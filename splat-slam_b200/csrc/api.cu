@@ -321,6 +321,27 @@ int splat_raster_knn_mean_dist2(int P, const float* points, void* scratch, float
     return SPLAT_OK;
 }
 
+int splat_raster_deform_points(int P, int K, const splat_raster_deform_keyframe* keyframes, const int* kf_ids,
+                               const float* intrinsics, int W, int H, float* table, float* xyz, float* rotation,
+                               float* scaling, void* stream) {
+    static_assert(SPLAT_DEFORM_TABLE_FLOATS == kDeformMaxKeyframes * 40, "table size");
+    if (P < 0 || K < 0) return SPLAT_ERR_SIZE;
+    if (P == 0 || K == 0) return SPLAT_OK;
+    if (!keyframes || !kf_ids || !table || !xyz || !rotation || !scaling) return SPLAT_ERR_ARG;
+    if ((reinterpret_cast<uintptr_t>(rotation) & 15u) != 0) return SPLAT_ERR_ARG;
+    std::vector<DeformKeyframe> kfs((size_t)K);
+    for (int k = 0; k < K; ++k) {
+        const splat_raster_deform_keyframe& in = keyframes[k];
+        if (!in.w2c_old || !in.w2c_new) return SPLAT_ERR_ARG;
+        if (!in.rigid && (!in.depth_new || !in.depth_old || !intrinsics || W <= 0 || H <= 0)) return SPLAT_ERR_ARG;
+        kfs[(size_t)k] = DeformKeyframe{in.w2c_old, in.w2c_new, in.depth_new, in.depth_old, in.frame_idx, in.rigid};
+    }
+    g_launches += launch_deform_points(P, K, kfs.data(), kf_ids, intrinsics, W, H, table, xyz, rotation, scaling,
+                                       (cudaStream_t)stream);
+    SPLAT_CUDA_CHECK_LAUNCH();
+    return SPLAT_OK;
+}
+
 int splat_raster_debug_views(int P, int R, int W, int H, void* geom, void* binning, void* image,
                              splat_raster_views* out) {
     if (!out || P < 0 || R < 0 || W <= 0 || H <= 0) return SPLAT_ERR_ARG;

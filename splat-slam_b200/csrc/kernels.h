@@ -65,6 +65,14 @@ int launch_visibility_count(int P, int K, const int* const* n_touched, long long
 // knn.cu
 size_t knn_scratch_bytes(size_t P);
 int launch_knn_mean_dist2(int P, const float* points, void* scratch, float* mean_dist2, cudaStream_t s);   // -> launches
+// deform.cu
+constexpr int kDeformMaxKeyframes = 64;   // keyframes per launch pair (kernel-parameter space)
+struct DeformKeyframe {
+    const float* w2c_old; const float* w2c_new; const float* depth_new; const float* depth_old;
+    int frame_idx; int rigid;
+};
+int launch_deform_points(int P, int K, const DeformKeyframe* kfs, const int* kf_ids, const float* intrinsics, int W, int H,
+                         float* table, float* xyz, float* rotation, float* scaling, cudaStream_t s);     // -> launches
 // render.cu
 void launch_render_forward(int W, int H, int grid_x, int grid_y, const uint2* ranges, const float* records,
                            const float* bg, float* final_T, uint32_t* n_contrib, float* out_color, float* out_depth,
