@@ -146,6 +146,20 @@ int splat_raster_mapping_loss(int W, int H, const float* image, const float* dep
                               float rgb_boundary_threshold, int initialization, float* workspace, float* out,
                               float* dL_dimage, float* dL_ddepth, void* stream);
 
+/* Parameter activations of the Gaussian model in one launch each way. Replaces the properties
+ * get_scaling / get_rotation / get_opacity (thirdparty/gaussian_splatting/scene/gaussian_model.py:53-61,76-94):
+ *   scales = exp(raw_scaling) [P*3];  rotations = raw_rotation / max(||raw_rotation||, 1e-12) [P*4];
+ *   opacities = sigmoid(raw_opacity) [P].
+ * The backward takes the raw parameters again (nothing is saved) and the gradients w.r.t. the three outputs; any g_* may
+ * be NULL (treated as zero) and any d_* may be NULL (not wanted). rotation arrays must be 16-byte aligned. */
+int splat_raster_activations_forward(int P, const float* raw_scaling, const float* raw_rotation,
+                                     const float* raw_opacity, float* scales, float* rotations, float* opacities,
+                                     void* stream);
+int splat_raster_activations_backward(int P, const float* raw_scaling, const float* raw_rotation,
+                                      const float* raw_opacity, const float* g_scales, const float* g_rotations,
+                                      const float* g_opacities, float* d_scaling, float* d_rotation, float* d_opacity,
+                                      void* stream);
+
 /* Fused Adam step over a list of tensors in one launch per 32 tensors (the step after backward).
  * Replaces `self.gaussians.optimizer.step()` / `self.keyframe_optimizers.step()` (src/mapper.py:557-562), i.e.
  * torch.optim.Adam as configured in thirdparty/gaussian_splatting/scene/gaussian_model.py:264-302 (one lr per group,

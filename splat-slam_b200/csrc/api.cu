@@ -254,6 +254,37 @@ int splat_raster_mapping_loss(int W, int H, const float* image, const float* dep
     return SPLAT_OK;
 }
 
+int splat_raster_activations_forward(int P, const float* raw_scaling, const float* raw_rotation,
+                                     const float* raw_opacity, float* scales, float* rotations, float* opacities,
+                                     void* stream) {
+    if (P < 0) return SPLAT_ERR_SIZE;
+    if (P == 0) return SPLAT_OK;
+    if (!raw_scaling || !raw_rotation || !raw_opacity || !scales || !rotations || !opacities) return SPLAT_ERR_ARG;
+    if (((reinterpret_cast<uintptr_t>(raw_rotation) | reinterpret_cast<uintptr_t>(rotations)) & 15u) != 0) return SPLAT_ERR_ARG;
+    launch_activations_forward(P, raw_scaling, raw_rotation, raw_opacity, scales, rotations, opacities,
+                               (cudaStream_t)stream);
+    g_launches += 1;
+    SPLAT_CUDA_CHECK_LAUNCH();
+    return SPLAT_OK;
+}
+
+int splat_raster_activations_backward(int P, const float* raw_scaling, const float* raw_rotation,
+                                      const float* raw_opacity, const float* g_scales, const float* g_rotations,
+                                      const float* g_opacities, float* d_scaling, float* d_rotation, float* d_opacity,
+                                      void* stream) {
+    if (P < 0) return SPLAT_ERR_SIZE;
+    if (P == 0) return SPLAT_OK;
+    if (!raw_scaling || !raw_rotation || !raw_opacity) return SPLAT_ERR_ARG;
+    uintptr_t bits = reinterpret_cast<uintptr_t>(raw_rotation) | reinterpret_cast<uintptr_t>(g_rotations) |
+                     reinterpret_cast<uintptr_t>(d_rotation);
+    if ((bits & 15u) != 0) return SPLAT_ERR_ARG;
+    launch_activations_backward(P, raw_scaling, raw_rotation, raw_opacity, g_scales, g_rotations, g_opacities, d_scaling,
+                                d_rotation, d_opacity, (cudaStream_t)stream);
+    g_launches += 1;
+    SPLAT_CUDA_CHECK_LAUNCH();
+    return SPLAT_OK;
+}
+
 int splat_raster_adam_step(int num_segments, const splat_raster_adam_segment* segments, int zero_grads, void* stream) {
     if (num_segments < 0 || (num_segments > 0 && !segments)) return SPLAT_ERR_ARG;
     std::vector<AdamSegment> segs;

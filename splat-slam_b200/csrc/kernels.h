@@ -73,6 +73,12 @@ struct DeformKeyframe {
 };
 int launch_deform_points(int P, int K, const DeformKeyframe* kfs, const int* kf_ids, const float* intrinsics, int W, int H,
                          float* table, float* xyz, float* rotation, float* scaling, cudaStream_t s);     // -> launches
+// activations.cu
+void launch_activations_forward(int P, const float* raw_scaling, const float* raw_rotation, const float* raw_opacity,
+                                float* scales, float* rotations, float* opacities, cudaStream_t s);
+void launch_activations_backward(int P, const float* raw_scaling, const float* raw_rotation, const float* raw_opacity,
+                                 const float* g_scales, const float* g_rotations, const float* g_opacities,
+                                 float* d_scaling, float* d_rotation, float* d_opacity, cudaStream_t s);
 // render.cu
 void launch_render_forward(int W, int H, int grid_x, int grid_y, const uint2* ranges, const float* records,
                            const float* bg, float* final_T, uint32_t* n_contrib, float* out_color, float* out_depth,

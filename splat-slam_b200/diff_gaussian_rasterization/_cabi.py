@@ -36,7 +36,7 @@ EXPORTS = (
     "splat_raster_mapping_loss_blocks", "splat_raster_mapping_loss", "splat_raster_adam_step",
     "splat_raster_densify_stats", "splat_raster_visibility_count",
     "splat_raster_knn_scratch_bytes", "splat_raster_knn_mean_dist2",
-    "splat_raster_deform_points",
+    "splat_raster_deform_points", "splat_raster_activations_forward", "splat_raster_activations_backward",
 )
 
 
