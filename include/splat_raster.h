@@ -57,6 +57,13 @@ int splat_raster_forward_preprocess(
     float tan_fovx, float tan_fovy, int prefiltered,
     int* radii, int* n_touched, void* geom, int* num_rendered_host, void* stream);
 
+/* Blocks the calling host thread until the num_rendered written by its last splat_raster_forward_preprocess call on
+ * the current device has reached `num_rendered_host` (which must then be pinned host memory). The preprocess call
+ * hands the count over right after its first kernel, so this returns while the per-Gaussian depth sort it also
+ * enqueued is still running; a plain stream synchronisation gives the same value later. The reference blocks in a
+ * 4-byte cudaMemcpy after its scan (DGR/cuda_rasterizer/rasterizer_impl.cu:284). */
+int splat_raster_forward_wait(void);
+
 /* Forward, stage 2 of 2: key generation, 64-bit (tile|depth) radix sort, tile ranges, render.
  * Replaces duplicateWithKeys, cub::DeviceRadixSort::SortPairs, identifyTileRanges and FORWARD::render
  * (DGR/cuda_rasterizer/rasterizer_impl.cu:286-341, forward.cu:263-392).

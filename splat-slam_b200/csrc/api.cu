@@ -11,6 +11,21 @@ using namespace splat;
 namespace {
 inline int grid_dim(int v) { return (v + SPLAT_TILE - 1) / SPLAT_TILE; }
 
+// One event per host thread and device marks the point where num_rendered has reached pinned host memory
+// (splat_raster_forward_preprocess records it, splat_raster_forward_wait waits on it).
+constexpr int kMaxDevices = 64;
+thread_local cudaEvent_t t_handoff[kMaxDevices];
+thread_local bool t_handoff_recorded[kMaxDevices];
+cudaEvent_t handoff_event() {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= kMaxDevices) return nullptr;
+    if (!t_handoff_recorded[dev]) {
+        if (cudaEventCreateWithFlags(&t_handoff[dev], cudaEventDisableTiming) != cudaSuccess) return nullptr;
+        t_handoff_recorded[dev] = true;
+    }
+    return t_handoff[dev];
+}
+
 // ---- diagnostics: kernel-launch counter and optional per-stage CUDA-event timing ------------------------
 enum Stage { ST_PREPROCESS = 0, ST_SCAN, ST_DUP, ST_SORT, ST_RECORDS, ST_RENDER_FWD, ST_ZERO, ST_RENDER_BWD,
              ST_PREPROCESS_BWD, ST_COUNT };
@@ -113,19 +128,34 @@ int splat_raster_forward_preprocess(int P, int D, int M, int W, int H, const flo
     p.cov3D_precomp = cov3D_precomp; p.colors_precomp = colors_precomp;
     p.viewmatrix = viewmatrix; p.projmatrix = projmatrix; p.campos = campos;
     p.radii = radii; p.n_touched = n_touched;
+    cudaMemsetAsync(g.num_rendered, 0, 4 * sizeof(uint32_t), s);     // word 1: instance total summed by preprocess
     prof_begin(ST_PREPROCESS, s);
     launch_preprocess_forward(p, g, s);
     prof_end(ST_PREPROCESS, s, 1);
     SPLAT_CUDA_CHECK_LAUNCH();
+    if (num_rendered_host) {
+        // hand R to the host now; the depth sort below runs while the caller sizes its binning buffer
+        cudaError_t e = cudaMemcpyAsync(num_rendered_host, g.num_rendered + 1, sizeof(int), cudaMemcpyDeviceToHost, s);
+        if (e != cudaSuccess) return (int)e;
+        cudaEvent_t ev = handoff_event();
+        if (ev) {
+            e = cudaEventRecord(ev, s);
+            if (e != cudaSuccess) return (int)e;
+        }
+    }
     prof_begin(ST_SCAN, s);
     launch_depth_sort_and_offsets(P, g, s);   // 2 histogram kernels + 4 sort passes + block sums + scan
     prof_end(ST_SCAN, s, 8);
     SPLAT_CUDA_CHECK_LAUNCH();
-    if (num_rendered_host) {
-        cudaError_t e = cudaMemcpyAsync(num_rendered_host, g.num_rendered, sizeof(int), cudaMemcpyDeviceToHost, s);
-        if (e != cudaSuccess) return (int)e;
-    }
     return SPLAT_OK;
+}
+
+int splat_raster_forward_wait(void) {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= kMaxDevices) return SPLAT_ERR_ARG;
+    if (!t_handoff_recorded[dev]) return SPLAT_OK;
+    const cudaError_t e = cudaEventSynchronize(t_handoff[dev]);
+    return e == cudaSuccess ? SPLAT_OK : (int)e;
 }
 
 int splat_raster_forward_render(int P, int R, int W, int H, const float* background, const float* colors_precomp,

@@ -139,6 +139,20 @@ preprocess_forward_kernel(int P, int D, int M,
         g.dkey[idx] = tiles ? __float_as_uint(tz_out) : 0xFFFFFFFFu;
         g.order[idx] = (uint32_t)idx;
     }
+    // R = total instances, available as soon as this kernel ends: the host reads it back while the depth sort runs
+    // instead of after it (the reference learns it only after its scan, rasterizer_impl.cu:280-284)
+    __shared__ uint32_t s_tiles[kPreBlock / 32];
+    uint32_t sum = tiles;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+    if ((threadIdx.x & 31) == 0) s_tiles[threadIdx.x >> 5] = sum;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint32_t total = 0;
+#pragma unroll
+        for (int w = 0; w < kPreBlock / 32; ++w) total += s_tiles[w];
+        if (total) atomicAdd(g.num_rendered + 1, total);
+    }
 }
 
 __global__ void mark_visible_kernel(int P, const float* __restrict__ means3D, const float* __restrict__ viewmatrix,

@@ -115,7 +115,7 @@ def _forward_impl(S, means3D, sh, colors_precomp, opacities, scales, rotations, 
                 _cabi.ptr(colors_precomp), _cabi.ptr(view), _cabi.ptr(proj), _cabi.ptr(campos), float(S.tanfovx),
                 float(S.tanfovy), int(bool(S.prefiltered)), radii.data_ptr(), n_touched.data_ptr(), geom.data_ptr(),
                 host_R.data_ptr(), stream), "forward_preprocess")
-            torch.cuda.current_stream(dev).synchronize()
+            _cabi.check(L.splat_raster_forward_wait(), "forward_wait")    # returns while the depth sort still runs
             rendered = int(host_R.item())
         binning = torch.empty((L.splat_raster_binning_bytes(rendered),), dtype=torch.uint8, device=dev)
         _cabi.check(L.splat_raster_forward_render(

@@ -30,7 +30,7 @@ class _Views(ctypes.Structure):
 
 EXPORTS = (
     "splat_raster_abi_version", "splat_raster_geom_bytes", "splat_raster_image_bytes", "splat_raster_binning_bytes",
-    "splat_raster_forward_preprocess", "splat_raster_forward_render", "splat_raster_backward",
+    "splat_raster_forward_preprocess", "splat_raster_forward_wait", "splat_raster_forward_render", "splat_raster_backward",
     "splat_raster_mark_visible", "splat_raster_debug_views", "splat_raster_launch_count", "splat_raster_profile",
     "splat_raster_stage_count", "splat_raster_stage_name", "splat_raster_profile_read",
     "splat_raster_mapping_loss_blocks", "splat_raster_mapping_loss", "splat_raster_adam_step",
@@ -60,6 +60,8 @@ def lib() -> ctypes.CDLL:
     L.splat_raster_forward_preprocess.restype = c_int
     L.splat_raster_forward_preprocess.argtypes = [c_int] * 5 + [P, P, c_float, P, P, P, P, P, P, P, P, c_float, c_float,
                                                                 c_int, P, P, P, P, P]
+    L.splat_raster_forward_wait.restype = c_int
+    L.splat_raster_forward_wait.argtypes = []
     L.splat_raster_forward_render.restype = c_int
     L.splat_raster_forward_render.argtypes = [c_int] * 4 + [P] * 11
     L.splat_raster_backward.restype = c_int
