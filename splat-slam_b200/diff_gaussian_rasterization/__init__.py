@@ -17,6 +17,7 @@ Host code stays Python/PyTorch: it allocates tensors, selects device + current s
 """
 from __future__ import annotations
 
+import threading
 from typing import NamedTuple
 
 import torch
@@ -55,17 +56,20 @@ def rasterize_gaussians(means3D, means2D, sh, colors_precomp, opacities, scales,
 
 
 class _PinnedInt:
-    """One pinned int32 per device for the num_rendered hand-off (the reference's blocking 4-byte cudaMemcpy,
-    DGR/cuda_rasterizer/rasterizer_impl.cu:284)."""
-    _slots = {}
+    """One pinned int32 per device and host thread for the num_rendered hand-off (the reference's blocking 4-byte
+    cudaMemcpy, DGR/cuda_rasterizer/rasterizer_impl.cu:284). A thread reads its slot before it enqueues the next
+    forward, so views issued on several streams by one thread can share it; threads must not."""
+    _local = threading.local()
 
     @classmethod
     def get(cls, device):
+        slots = getattr(cls._local, "slots", None)
+        if slots is None:
+            slots = cls._local.slots = {}
         key = (device.type, device.index)
-        t = cls._slots.get(key)
+        t = slots.get(key)
         if t is None:
-            t = torch.zeros(1, dtype=torch.int32).pin_memory()
-            cls._slots[key] = t
+            t = slots[key] = torch.zeros(1, dtype=torch.int32).pin_memory()
         return t
 
 
