@@ -119,9 +119,19 @@ preprocess_backward_kernel(BwdParams p, GeomState g, float* __restrict__ tau_par
         float4 acc0 = make_float4(0, 0, 0, 0), acc1 = acc0, acc2 = acc0;
         if (vis) {
             const float4* acc = reinterpret_cast<const float4*>(p.grad_accum) + 3 * (size_t)idx;
-            acc0 = acc[0];   // mean2D.x, mean2D.y, conic.x, conic.y
-            acc1 = acc[1];   // conic.w, opacity, r, g
+            acc0 = acc[0];   // moments of u = G dL/dalpha over the pixels: sum u dx, sum u dy, sum u dx^2, sum u dx dy
+            acc1 = acc[1];   // sum u dy^2, sum u (= dL/dopacity), r, g
             acc2 = acc[2];   // b, depth, -, -
+            {   // moments -> dL/dmean2D (NDC units), dL/dconic: the per-Gaussian factors the render backward left out
+                // (backward.cu:745-770: dL_dG = opacity * dL_dalpha, dG_ddel = -G (conic . d), ddel_dx = 0.5 W)
+                const float4 co = g.conic_opacity[idx];
+                const float sx = acc0.x, sy = acc0.y, ho = -0.5f * co.w;
+                acc0.x = ho * (float)p.W * (co.x * sx + co.y * sy);
+                acc0.y = ho * (float)p.H * (co.z * sy + co.y * sx);
+                acc0.z *= ho;
+                acc0.w *= ho;
+                acc1.x *= ho;
+            }
             const f3 m = mk(p.means3D[3 * idx], p.means3D[3 * idx + 1], p.means3D[3 * idx + 2]);
             const float* cov3D = p.cov3D_precomp ? p.cov3D_precomp + 6 * (size_t)idx : g.cov3D + 6 * (size_t)idx;
 

@@ -285,7 +285,7 @@ render_backward_kernel(int W, int H, int grid_x, const uint2* __restrict__ range
     }
 
     // which of the 10 reduced terms this lane ends up holding (see warp_reduce10), and where it goes in the
-    // packed accumulator {mean2D.x, mean2D.y, conic.x, conic.y, conic.w, opacity, r, g, b, depth, -, -}
+    // packed accumulator {sum u dx, sum u dy, sum u dx^2, sum u dx dy, sum u dy^2, sum u, r, g, b, depth, -, -}
     const int inner3 = ((lane >> 2) & 1) * 2 + ((lane >> 1) & 1);
     const int inner5 = ((lane >> 3) & 1) * 3 + inner3;
     const int my_k = ((lane >> 4) & 1) * 5 + inner5;
@@ -303,7 +303,6 @@ render_backward_kernel(int W, int H, int grid_x, const uint2* __restrict__ range
     const float bg_dot_dpixel = bg[0] * dLp0 + bg[1] * dLp1 + bg[2] * dLp2;
     float acc0 = 0.0f, acc1 = 0.0f, acc2 = 0.0f, accd = 0.0f;         // accum_rec, accum_rec_depth
     float last_alpha = 0.0f, lc0 = 0.0f, lc1 = 0.0f, lc2 = 0.0f, last_depth = 0.0f;
-    const float ddelx_dx = 0.5f * W, ddely_dy = 0.5f * H;               // backward.cu:643-644
 
     // nothing in this warp ever blended anything -> the warp only helps with barriers
     const int warp_last = __reduce_max_sync(0xffffffffu, last_contributor);
@@ -351,17 +350,20 @@ render_backward_kernel(int W, int H, int grid_x, const uint2* __restrict__ range
                 // alpha also scales how much background shows through (backward.cu:736-743)
                 dL_dalpha += (-T_final * inv) * bg_dot_dpixel;
 
-                const float dL_dG = r1.y * dL_dalpha;
-                const float gdx = G * dx, gdy = G * dy;
-                const float dG_ddelx = -gdx * r0.z - gdy * r0.w;
-                const float dG_ddely = -gdy * r1.x - gdx * r0.w;
+                // Everything that is constant per Gaussian (opacity, conic, the -0.5 and the NDC scale) is factored out
+                // of the pixel sum: the warp reduces the moments of u = G * dL/dalpha over its pixels,
+                //   sum u dx, sum u dy, sum u dx^2, sum u dx dy, sum u dy^2, sum u,
+                // and the per-Gaussian backward turns them into dL/dmean2D, dL/dconic, dL/dopacity
+                // (backward.cu:745-770; preprocess_bwd.cu: moments_to_gradients).
+                const float u = G * dL_dalpha;
+                const float ux = u * dx, uy = u * dy;
                 float v[10];
-                v[0] = dL_dG * dG_ddelx * ddelx_dx;
-                v[1] = dL_dG * dG_ddely * ddely_dy;
-                v[2] = -0.5f * gdx * dx * dL_dG;
-                v[3] = -0.5f * gdx * dy * dL_dG;
-                v[4] = -0.5f * gdy * dy * dL_dG;
-                v[5] = G * dL_dalpha;
+                v[0] = ux;
+                v[1] = uy;
+                v[2] = ux * dx;
+                v[3] = ux * dy;
+                v[4] = uy * dy;
+                v[5] = u;
                 v[6] = dchannel_dcolor * dLp0;
                 v[7] = dchannel_dcolor * dLp1;
                 v[8] = dchannel_dcolor * dLp2;
