@@ -55,7 +55,8 @@ def parse():
     ap.add_argument("--views", type=int, default=VIEWS_PER_RANK)
     ap.add_argument("--camera", default=CAMERA)
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--streams", type=int, default=3,
+    ap.add_argument("--priority-lanes", type=int, default=1, help="1: short kernels on a high-priority side stream")
+    ap.add_argument("--streams", type=int, default=5,
                     help="views of a step are issued round-robin on this many CUDA streams (ours only; the reference "
                          "extension launches on the legacy default stream and always runs with 1)")
     return ap.parse_args()
@@ -152,7 +153,8 @@ class Workload:
         self.rho = [torch.zeros(3, device=device, requires_grad=True) for _ in self.view_ids]
         self.means2D = torch.zeros_like(self.params["means3D"], requires_grad=True)
         # e2e leg: double-buffered device staging filled by a copy stream, so the next view's H2D overlaps compute
-        self.streams = ViewStreams(device, args.streams if mod.__name__ == "diff_gaussian_rasterization" else 1)
+        self.streams = ViewStreams(device, args.streams if mod.__name__ == "diff_gaussian_rasterization" else 1,
+                                   priority_lanes=bool(args.priority_lanes))
         self.nbuf = max(2, len(self.streams) + 1)      # one staging buffer per view in flight, plus the one being filled
         self.stage_mats = [torch.empty_like(self.d_mats[0]) for _ in range(self.nbuf)] if self.d_mats else None
         self.stage_up = [torch.empty_like(self.d_up) for _ in range(self.nbuf)]
@@ -326,6 +328,7 @@ def main():
     launches0 = 0
     if kind == "ours":
         from diff_gaussian_rasterization import _cabi
+        _cabi.priority_lanes(bool(args.priority_lanes) and args.streams > 1)
     ms_value = timed(wl.step_resident, args.steps, args.warmup, device, ref_world)
     if kind == "ours":      # kernels of this library per step, counted by the library itself, x timed steps
         _cabi.launch_count(reset=True)
@@ -395,7 +398,8 @@ def main():
                                      f"{wl.flat.flat.numel() * 4} B/step" if ref_world > 1 else "none (1 GPU)",
                        "l2": "inputs larger than L2: ~0.4 GB of state per view, 10 distinct views per step",
                        "resident": "Gaussian parameters stay in HBM (model state)",
-                       "streams": n_streams},
+                       "streams": n_streams,
+                       "priority_lanes": bool(args.priority_lanes) and n_streams > 1 and kind == "ours"},
             "e2e": {"value": e2e, "unit": "it/s", "h2d_bytes_per_step": wl.h2d_bytes_per_step(),
                     "d2h_bytes_per_step": wl.d2h_bytes_per_step(), "ms_per_step": ms_e2e / args.steps},
             "gpu_launches": int(launches0) if kind == "ours" else 0,

@@ -236,6 +236,12 @@ int splat_raster_deform_points(int P, int K, const splat_raster_deform_keyframe*
                                const float* intrinsics, int W, int H, float* table, float* xyz, float* rotation,
                                float* scaling, void* stream);
 
+/* Scheduling option, off by default: run the short latency-bound kernels of a forward (everything except the two
+ * render kernels) on a highest-priority side stream, ordered against the caller's stream with events, so that with
+ * several views in flight on different streams they are not queued behind another view's render CTAs.
+ * enable: 1 on, 0 off, < 0 query only. Returns the previous setting. No counterpart in the reference. */
+int splat_raster_priority_lanes(int enable);
+
 /* Test/diagnostic view into the opaque buffers (device pointers into the caller's buffers; layout is private).
  * Mirrors what the parity harness carves out of the reference's buffers (rasterizer_impl.cu:155-194). */
 typedef struct splat_raster_views {

@@ -4,6 +4,9 @@
 #include "kernels.h"
 
 #include <cmath>
+#include <map>
+#include <mutex>
+#include <utility>
 #include <vector>
 
 using namespace splat;
@@ -26,6 +29,57 @@ cudaEvent_t handoff_event() {
     return t_handoff[dev];
 }
 
+// Optional high-priority side lane for the short, latency-bound kernels of a forward (preprocess, the sort passes, key
+// emission, record gather). With several views in flight on different streams the two render kernels keep every SM
+// busy for hundreds of microseconds; CTAs of a higher-priority stream are scheduled first whenever a slot frees up, so
+// a view's ~20 small kernels slip through another view's render instead of queueing behind its remaining CTAs.
+// Ordering with the caller's stream is kept by an event pair (fork at entry, join before the render kernel / return).
+struct Lane {
+    cudaStream_t hp = nullptr;
+    cudaEvent_t fork = nullptr, join = nullptr;
+};
+int g_priority_lanes = 0;
+bool profiling_enabled();
+std::mutex g_lane_mutex;
+std::map<std::pair<int, cudaStream_t>, Lane> g_lanes;
+
+cudaStream_t lane_begin(cudaStream_t s) {
+    if (!g_priority_lanes || profiling_enabled()) return s;
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return s;
+    Lane lane;
+    {
+        std::lock_guard<std::mutex> lock(g_lane_mutex);
+        Lane& l = g_lanes[std::make_pair(dev, s)];
+        if (!l.hp) {
+            int lo = 0, hi = 0;
+            cudaDeviceGetStreamPriorityRange(&lo, &hi);       // hi is the numerically lowest = greatest priority
+            if (cudaStreamCreateWithPriority(&l.hp, cudaStreamNonBlocking, hi) != cudaSuccess ||
+                cudaEventCreateWithFlags(&l.fork, cudaEventDisableTiming) != cudaSuccess ||
+                cudaEventCreateWithFlags(&l.join, cudaEventDisableTiming) != cudaSuccess) {
+                l = Lane();
+                return s;
+            }
+        }
+        lane = l;
+    }
+    if (cudaEventRecord(lane.fork, s) != cudaSuccess || cudaStreamWaitEvent(lane.hp, lane.fork, 0) != cudaSuccess) return s;
+    return lane.hp;
+}
+
+void lane_end(cudaStream_t s, cudaStream_t used) {
+    if (used == s) return;
+    int dev = 0;
+    cudaGetDevice(&dev);
+    Lane lane;
+    {
+        std::lock_guard<std::mutex> lock(g_lane_mutex);
+        lane = g_lanes[std::make_pair(dev, s)];
+    }
+    cudaEventRecord(lane.join, used);
+    cudaStreamWaitEvent(s, lane.join, 0);
+}
+
 // ---- diagnostics: kernel-launch counter and optional per-stage CUDA-event timing ------------------------
 enum Stage { ST_PREPROCESS = 0, ST_SCAN, ST_DUP, ST_SORT, ST_RECORDS, ST_RENDER_FWD, ST_ZERO, ST_RENDER_BWD,
              ST_PREPROCESS_BWD, ST_COUNT };
@@ -34,6 +88,7 @@ const char* kStageNames[ST_COUNT] = {"preprocess_forward", "depth_sort_and_offse
                                      "render_backward", "preprocess_backward"};
 unsigned long long g_launches = 0;
 int g_prof = 0;
+bool profiling_enabled() { return g_prof != 0; }
 int g_prof_dev = -1;
 cudaEvent_t g_ev[ST_COUNT][2];
 bool g_pending[ST_COUNT];
@@ -105,7 +160,8 @@ int splat_raster_forward_preprocess(int P, int D, int M, int W, int H, const flo
                                     void* geom, int* num_rendered_host, void* stream) {
     if (P < 0 || W <= 0 || H <= 0 || D < 0 || D > 3) return SPLAT_ERR_SIZE;
     if (!geom || !viewmatrix || !projmatrix) return SPLAT_ERR_ARG;
-    cudaStream_t s = (cudaStream_t)stream;
+    const cudaStream_t caller = (cudaStream_t)stream;
+    cudaStream_t s = caller;
     GeomState g = GeomState::carve(geom, (size_t)P, nullptr);
     if (P == 0) {
         cudaMemsetAsync(g.num_rendered, 0, sizeof(uint32_t), s);
@@ -128,6 +184,7 @@ int splat_raster_forward_preprocess(int P, int D, int M, int W, int H, const flo
     p.cov3D_precomp = cov3D_precomp; p.colors_precomp = colors_precomp;
     p.viewmatrix = viewmatrix; p.projmatrix = projmatrix; p.campos = campos;
     p.radii = radii; p.n_touched = n_touched;
+    s = lane_begin(caller);
     cudaMemsetAsync(g.num_rendered, 0, 4 * sizeof(uint32_t), s);     // word 1: instance total summed by preprocess
     prof_begin(ST_PREPROCESS, s);
     launch_preprocess_forward(p, g, s);
@@ -146,8 +203,15 @@ int splat_raster_forward_preprocess(int P, int D, int M, int W, int H, const flo
     prof_begin(ST_SCAN, s);
     launch_depth_sort_and_offsets(P, g, s);   // 2 histogram kernels + 4 sort passes + block sums + scan
     prof_end(ST_SCAN, s, 8);
+    lane_end(caller, s);
     SPLAT_CUDA_CHECK_LAUNCH();
     return SPLAT_OK;
+}
+
+int splat_raster_priority_lanes(int enable) {
+    const int was = g_priority_lanes;
+    if (enable >= 0) g_priority_lanes = enable ? 1 : 0;
+    return was;
 }
 
 int splat_raster_forward_wait(void) {
@@ -164,7 +228,8 @@ int splat_raster_forward_render(int P, int R, int W, int H, const float* backgro
     if (P < 0 || R < 0 || W <= 0 || H <= 0) return SPLAT_ERR_SIZE;
     if (!geom || !binning || !image || !background || !out_color || !out_depth || !out_opacity) return SPLAT_ERR_ARG;
     if (P > 0 && (!radii || !n_touched)) return SPLAT_ERR_ARG;
-    cudaStream_t s = (cudaStream_t)stream;
+    const cudaStream_t caller = (cudaStream_t)stream;
+    cudaStream_t s = lane_begin(caller);     // key emission, tile sort and record gather on the side lane, if enabled
     const int gx = grid_dim(W), gy = grid_dim(H);
     GeomState g = GeomState::carve(geom, (size_t)P, nullptr);
     BinningState b = BinningState::carve(binning, (size_t)R, nullptr);
@@ -190,6 +255,8 @@ int splat_raster_forward_render(int P, int R, int W, int H, const float* backgro
     prof_begin(ST_RECORDS, s);
     launch_ranges_and_records(R, gx * gy, g, b, im.ranges, s);
     prof_end(ST_RECORDS, s, R > 0 ? 1 : 0);
+    lane_end(caller, s);
+    s = caller;
     SPLAT_CUDA_CHECK_LAUNCH();
     prof_begin(ST_RENDER_FWD, s);
     launch_render_forward(W, H, gx, gy, im.ranges, b.records, background, im.final_T, im.n_contrib, out_color,

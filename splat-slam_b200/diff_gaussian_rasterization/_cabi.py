@@ -36,7 +36,7 @@ EXPORTS = (
     "splat_raster_mapping_loss_blocks", "splat_raster_mapping_loss", "splat_raster_adam_step",
     "splat_raster_densify_stats", "splat_raster_visibility_count",
     "splat_raster_knn_scratch_bytes", "splat_raster_knn_mean_dist2",
-    "splat_raster_deform_points", "splat_raster_activations_forward", "splat_raster_activations_backward",
+    "splat_raster_deform_points", "splat_raster_activations_forward", "splat_raster_activations_backward", "splat_raster_priority_lanes",
 )
 
 
@@ -141,6 +141,15 @@ def debug_views(P, R, W, H, geom, binning, image):
     )
     assert dev == out["depths"].device
     return out
+
+
+def priority_lanes(enable: bool | None = None) -> bool:
+    """Run the short kernels of a forward on a high-priority side stream (see include/splat_raster.h). Returns the
+    previous setting; None only queries."""
+    L = lib()
+    L.splat_raster_priority_lanes.restype = c_int
+    L.splat_raster_priority_lanes.argtypes = [c_int]
+    return bool(L.splat_raster_priority_lanes(-1 if enable is None else int(bool(enable))))
 
 
 def launch_count(reset: bool = False) -> int:

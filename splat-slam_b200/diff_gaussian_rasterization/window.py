@@ -65,13 +65,19 @@ class ViewStreams:
     The views are independent until autograd accumulates their gradients, so issuing them on a few streams lets one
     view's latency-bound sort passes and its num_rendered hand-off (the one host sync of a forward) hide under another
     view's render kernels. `fork()` makes the side streams wait for the work queued so far, `join()` makes the
-    caller's stream wait for all of them. With n <= 1 everything stays on the caller's stream."""
+    caller's stream wait for all of them. With n <= 1 everything stays on the caller's stream.
+    Measured on one B200 (bench workload): 1 stream 676 it/s, 3 streams 767, 5 streams with priority lanes 823."""
 
-    def __init__(self, device, n: int = 3):
+    def __init__(self, device, n: int = 5, priority_lanes: bool = True):
         self.device = torch.device(device)
         self.streams = [torch.cuda.Stream(device=self.device) for _ in range(n)] if n > 1 else []
         if self.streams:   # accumulation into the shared leaves deliberately crosses streams; autograd orders it
             torch.autograd.graph.set_warn_on_accumulate_grad_stream_mismatch(False)
+            if priority_lanes:
+                # the ~20 short kernels of each forward go to a high-priority side stream so that they are not
+                # queued behind the render CTAs of the other views in flight (library-wide switch)
+                from . import _cabi
+                _cabi.priority_lanes(True)
 
     def __len__(self):
         return len(self.streams)

@@ -324,9 +324,30 @@ def test_window_step_on_several_streams_matches_one_stream():
             return color, depth
 
         for _ in range(2):          # second pass re-uses the cached allocator blocks across streams
-            window_step(render_view, lambda v: (Wc, Wd), flat, n_views, streams=ViewStreams("cuda:0", n_streams))
+            window_step(render_view, lambda v: (Wc, Wd), flat, n_views,
+                        streams=ViewStreams("cuda:0", n_streams, priority_lanes=True))
             torch.cuda.synchronize()
         res.append((flat.flat.clone(), torch.stack([t.grad for t in theta]), torch.stack([r.grad for r in rho]),
                     means2D.grad.clone()))
     for a, b in zip(res[1], res[0]):
         assert T.rel_err(a, b) <= 1e-4
+
+
+@needs_ref
+def test_priority_lanes_keep_the_chain_bit_exact():
+    """With the short kernels on the high-priority side stream the forward is the same computation, event-ordered."""
+    from diff_gaussian_rasterization import _cabi
+    was = _cabi.priority_lanes(True)
+    try:
+        assert _cabi.priority_lanes(None) is True
+        for name in ("ragged_sh1_bg", "small_sh3", "tum_200k"):
+            case = _make(CASES[name])
+            with torch.cuda.stream(torch.cuda.Stream()):
+                ours = T.ours_forward_with_intermediates(case)
+                a = T.run_module(T.load_ours(), case)
+            torch.cuda.synchronize()
+            ref = T.ref_forward_with_intermediates(T.load_ref(), case)
+            T.compare_intermediates(ours, ref)
+            T.compare_outputs(a, T.run_module(T.load_ref(), case), exact_ints=True)
+    finally:
+        _cabi.priority_lanes(was)
