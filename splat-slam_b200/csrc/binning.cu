@@ -2,6 +2,7 @@
 // Together with radix_sort.cu this replaces cub::DeviceScan::InclusiveSum (DGR/cuda_rasterizer/rasterizer_impl.cu:280),
 // duplicateWithKeys (:70-111), cub::DeviceRadixSort::SortPairs (:303-311), cudaMemset + identifyTileRanges
 // (:313-321,116-138).
+#include <cstdio>
 #include "common.cuh"
 #include "kernels.h"
 
@@ -83,6 +84,11 @@ void launch_depth_sort_and_offsets(int P, const GeomState& g, cudaStream_t s) {
 __global__ void __launch_bounds__(kPreBlock)
 duplicate_with_keys_kernel(int P, int grid_x, int grid_y, const int* __restrict__ radii, GeomState g,
                            uint32_t* __restrict__ tkeys_out, uint32_t* __restrict__ vals_out) {
+    // a depth sort whose look-back gave up must not go unnoticed: fail the stream loudly
+    if (blockIdx.x == 0 && threadIdx.x == 0 && *sort_error_flag(g.sort_scratch) != 0u) {
+        printf("splat_raster: depth sort look-back timed out\n");
+        __trap();
+    }
     __shared__ uint32_t s_incl[kPreBlock];
     __shared__ uint32_t s_rect[kPreBlock];   // x0 | y0 << 16
     __shared__ uint32_t s_w[kPreBlock];
@@ -153,7 +159,12 @@ void launch_duplicate_with_keys(int P, int grid_x, int grid_y, const int* radii,
 __global__ void __launch_bounds__(256)
 ranges_and_records_kernel(int R, const uint32_t* __restrict__ tkeys, const uint32_t* __restrict__ point_list,
                           const float4* __restrict__ gauss_rec, uint2* __restrict__ ranges,
-                          uint64_t* __restrict__ keys64, float4* __restrict__ records) {
+                          uint64_t* __restrict__ keys64, float4* __restrict__ records,
+                          const uint32_t* __restrict__ sort_error) {
+    if (blockIdx.x == 0 && threadIdx.x == 0 && *sort_error != 0u) {
+        printf("splat_raster: tile sort look-back timed out\n");
+        __trap();
+    }
     __shared__ float4 s_t[256 / 32][32 * 3];
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -190,7 +201,8 @@ void launch_ranges_and_records(int R, int tiles, const GeomState& g, const Binni
     cudaMemsetAsync(ranges, 0, sizeof(uint2) * (size_t)tiles, s);
     if (R <= 0) return;
     ranges_and_records_kernel<<<(R + 255) / 256, 256, 0, s>>>(R, b.tkey, b.point_list, g.rec, ranges, b.keys,
-                                                              reinterpret_cast<float4*>(b.records));
+                                                              reinterpret_cast<float4*>(b.records),
+                                                              sort_error_flag(b.sort_scratch));
 }
 
 }  // namespace splat

@@ -20,6 +20,9 @@ constexpr int kRadix = 1 << kRadixBits;
 
 // 32-bit words of scratch launch_sort_pairs needs for n pairs and up to 4 passes:
 // [4][256] digit histograms + 64 (tickets, error flag) + [4][ntiles][256] look-back tile states
+// where launch_sort_pairs leaves its "look-back timed out" flag inside the scratch (checked by the consuming kernel)
+__host__ __device__ inline const uint32_t* sort_error_flag(const uint32_t* scratch) { return scratch + 4 * kRadix + 8; }
+
 inline size_t sort_scratch_words(size_t n) {
     const size_t ntiles = (n + kSortTile - 1) / kSortTile;
     return 4 * kRadix + 64 + 4 * (ntiles ? ntiles : 1) * kRadix;
