@@ -160,6 +160,7 @@ class Workload:
         self.stage_up = [torch.empty_like(self.d_up) for _ in range(self.nbuf)]
         self.copy_stream = torch.cuda.Stream(device=device)
         self.ev_ready = [torch.cuda.Event() for _ in range(self.nbuf)]
+        self.ev_mats = [torch.cuda.Event() for _ in range(self.nbuf)]
         self.ev_free = [torch.cuda.Event() for _ in range(self.nbuf)]
         self.last = {}
 
@@ -170,12 +171,14 @@ class Workload:
             scale_modifier=1.0, viewmatrix=mats[0].view(4, 4), projmatrix=mats[1].view(4, 4),
             projmatrix_raw=mats[2].view(4, 4), sh_degree=0, campos=mats[3][:3], prefiltered=False, debug=False)
 
-    def render_backward(self, i, mats, up):
+    def render_backward(self, i, mats, up, up_ready=None):
         p = self.params
         rast = self.mod.GaussianRasterizer(raster_settings=self.settings(i, mats))
         color, radii, depth, opacity, n_touched = rast(
             means3D=p["means3D"], means2D=self.means2D, opacities=p["opacities"], shs=p["shs"], scales=p["scales"],
             rotations=p["rotations"], theta=self.theta[i], rho=self.rho[i])
+        if up_ready is not None:      # e2e leg: the upstream images are only needed from here on
+            torch.cuda.current_stream(self.device).wait_event(up_ready)
         torch.autograd.backward([color, depth], [up[:3], up[3:4]])
         self.last = dict(radii=radii, color=color, depth=depth)
         return color, depth
@@ -201,8 +204,9 @@ class Workload:
             with torch.cuda.stream(self.copy_stream):
                 self.copy_stream.wait_event(self.ev_free[b])       # the view that used this buffer is done
                 self.stage_mats[b].copy_(self.h_mats[i], non_blocking=True)
+                self.ev_mats[b].record(self.copy_stream)           # 256 B: the forward can start right away
                 self.stage_up[b].copy_(self.h_up, non_blocking=True)
-                self.ev_ready[b].record(self.copy_stream)
+                self.ev_ready[b].record(self.copy_stream)          # 13 MB: needed by the backward
 
         self.flat.zero_()
         lanes = max(1, len(self.streams))
@@ -218,10 +222,11 @@ class Workload:
                 prefetch(i + 1)
             with self.streams.view(i):
                 st = self.streams.stream(i)
-                st.wait_event(self.ev_ready[b])
-                color, depth = self.render_backward(i, self.stage_mats[b], self.stage_up[b])
-                acc[i % lanes] = (acc[i % lanes] + (color.detach() * self.stage_up[b][:3]).sum()
-                                  + (depth.detach() * self.stage_up[b][3:4]).sum())
+                st.wait_event(self.ev_mats[b])
+                color, depth = self.render_backward(i, self.stage_mats[b], self.stage_up[b], up_ready=self.ev_ready[b])
+                up = self.stage_up[b]
+                acc[i % lanes] = (acc[i % lanes] + torch.dot(color.detach().reshape(-1), up[:3].reshape(-1))
+                                  + torch.dot(depth.detach().reshape(-1), up[3:4].reshape(-1)))
                 self.ev_free[b].record(st)
         self.streams.join()
         self.flat.all_reduce()
