@@ -102,6 +102,9 @@ FULL_SIZE = {
     "replica_1M_sh0": dict(camera="replica", P=1_000_000, view_k=4),
     "tum_200k_view7": dict(camera="tum", P=200_000, view_k=7),
     "scannet_3M_sh3": dict(camera="scannet", P=3_000_000, sh_coeffs=16, sh_degree=3, view_k=2),
+    # many instances per Gaussian: R = 15 M (tile lists up to 6.6 k) and R = 53 M (tile lists up to 22 k)
+    "replica_1M_scale3": dict(camera="replica", P=1_000_000, view_k=3, scale_modifier=3.0),
+    "replica_2M_big_splats": dict(camera="replica", P=2_000_000, view_k=5, sigma_px=8.0),
 }
 
 
