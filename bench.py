@@ -372,8 +372,12 @@ def main():
                "duplicate_with_keys": 8 * Pn + 12 * V + 12 * R, "ranges_and_records": 12 * R + 44 * R + 48 * R}
         a_bytes = alg.get(dom, 0)
         ach = a_bytes / (stages[dom] * 1e-3) / 1e9
+        # dram__bytes_read.sum + dram__bytes_write.sum per launch from the ncu --set full capture of this workload
+        # (profiles/r01_render_final_summary.md); only valid for the default scene
+        default_scene = (args.camera == CAMERA and args.gaussians == P_GAUSS)
+        traffic = {"render_backward": 248.1e6, "render_forward": 174.8e6}.get(dom) if default_scene else None
         roofline = {"kernel": dom, "bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
-                    "traffic": None, "algorithmic_bytes_per_launch": a_bytes, "ms_per_launch": stages[dom],
+                    "traffic": traffic, "algorithmic_bytes_per_launch": a_bytes, "ms_per_launch": stages[dom],
                     "share_of_kernel_time": stages[dom] / total, "peak_source": peak_src,
                     "note": "render kernels reuse each 48-B record 256x; their limiter is FP32/SFU issue, shuffles and "
                             "L2 atomics, not HBM (SURVEY.md §8d) — see profiles/"}
