@@ -42,8 +42,10 @@ __device__ __forceinline__ f3 dnormvdv(f3 v, f3 dv) {
 }
 
 // SH backward (backward.cu:21-145): writes dL_dsh rows [0, M), returns dL/dmean through the view direction.
-__device__ f3 sh_backward(int deg, int M, const float* __restrict__ shs, f3 pos, f3 campos, uint8_t clamp_bits,
-                          f3 dL_dRGB, float* __restrict__ dL_dsh_out) {
+// Everything that READS the coefficients (the direction derivatives dRGB/dx,y,z) comes before the first write of a
+// gradient row, so `dL_dsh_out` may be the same memory as `shs` (the shared-memory staging row of the caller).
+__device__ f3 sh_backward(int deg, int M, const float* shs, f3 pos, f3 campos, uint8_t clamp_bits, f3 dL_dRGB,
+                          float* dL_dsh_out) {
     const f3 dir_orig = mk(pos.x - campos.x, pos.y - campos.y, pos.z - campos.z);
     const float inv_len = 1.0f / sqrtf(dot(dir_orig, dir_orig));
     const float x = dir_orig.x * inv_len, y = dir_orig.y * inv_len, z = dir_orig.z * inv_len;
@@ -52,39 +54,19 @@ __device__ f3 sh_backward(int deg, int M, const float* __restrict__ shs, f3 pos,
     if (clamp_bits & 1) dL_dRGB.x = 0.0f;
     if (clamp_bits & 2) dL_dRGB.y = 0.0f;
     if (clamp_bits & 4) dL_dRGB.z = 0.0f;
+    const float xx = x * x, yy = y * y, zz = z * z, xy = x * y, yz = y * z, xz = x * z;
     f3 dRGBdx = mk(0, 0, 0), dRGBdy = mk(0, 0, 0), dRGBdz = mk(0, 0, 0);
-    int written = 1;
-    out[0] = kB_SH_C0 * dL_dRGB;
     if (deg > 0) {
-        out[1] = (-kB_SH_C1 * y) * dL_dRGB;
-        out[2] = (kB_SH_C1 * z) * dL_dRGB;
-        out[3] = (-kB_SH_C1 * x) * dL_dRGB;
-        written = 4;
         dRGBdx = (-kB_SH_C1) * sh[3];
         dRGBdy = (-kB_SH_C1) * sh[1];
         dRGBdz = kB_SH_C1 * sh[2];
         if (deg > 1) {
-            const float xx = x * x, yy = y * y, zz = z * z, xy = x * y, yz = y * z, xz = x * z;
-            out[4] = (kB_SH_C2[0] * xy) * dL_dRGB;
-            out[5] = (kB_SH_C2[1] * yz) * dL_dRGB;
-            out[6] = (kB_SH_C2[2] * (2.f * zz - xx - yy)) * dL_dRGB;
-            out[7] = (kB_SH_C2[3] * xz) * dL_dRGB;
-            out[8] = (kB_SH_C2[4] * (xx - yy)) * dL_dRGB;
-            written = 9;
             dRGBdx = dRGBdx + (kB_SH_C2[0] * y) * sh[4] + (kB_SH_C2[2] * 2.f * -x) * sh[6] + (kB_SH_C2[3] * z) * sh[7] +
                      (kB_SH_C2[4] * 2.f * x) * sh[8];
             dRGBdy = dRGBdy + (kB_SH_C2[0] * x) * sh[4] + (kB_SH_C2[1] * z) * sh[5] + (kB_SH_C2[2] * 2.f * -y) * sh[6] +
                      (kB_SH_C2[4] * 2.f * -y) * sh[8];
             dRGBdz = dRGBdz + (kB_SH_C2[1] * y) * sh[5] + (kB_SH_C2[2] * 2.f * 2.f * z) * sh[6] + (kB_SH_C2[3] * x) * sh[7];
             if (deg > 2) {
-                out[9] = (kB_SH_C3[0] * y * (3.f * xx - yy)) * dL_dRGB;
-                out[10] = (kB_SH_C3[1] * xy * z) * dL_dRGB;
-                out[11] = (kB_SH_C3[2] * y * (4.f * zz - xx - yy)) * dL_dRGB;
-                out[12] = (kB_SH_C3[3] * z * (2.f * zz - 3.f * xx - 3.f * yy)) * dL_dRGB;
-                out[13] = (kB_SH_C3[4] * x * (4.f * zz - xx - yy)) * dL_dRGB;
-                out[14] = (kB_SH_C3[5] * z * (xx - yy)) * dL_dRGB;
-                out[15] = (kB_SH_C3[6] * x * (xx - 3.f * yy)) * dL_dRGB;
-                written = 16;
                 dRGBdx = dRGBdx + (kB_SH_C3[0] * 3.f * 2.f * xy) * sh[9] + (kB_SH_C3[1] * yz) * sh[10] +
                          (kB_SH_C3[2] * -2.f * xy) * sh[11] + (kB_SH_C3[3] * -3.f * 2.f * xz) * sh[12] +
                          (kB_SH_C3[4] * (-3.f * xx + 4.f * zz - yy)) * sh[13] + (kB_SH_C3[5] * 2.f * xz) * sh[14] +
@@ -99,16 +81,62 @@ __device__ f3 sh_backward(int deg, int M, const float* __restrict__ shs, f3 pos,
             }
         }
     }
+    int written = 1;
+    out[0] = kB_SH_C0 * dL_dRGB;
+    if (deg > 0) {
+        out[1] = (-kB_SH_C1 * y) * dL_dRGB;
+        out[2] = (kB_SH_C1 * z) * dL_dRGB;
+        out[3] = (-kB_SH_C1 * x) * dL_dRGB;
+        written = 4;
+        if (deg > 1) {
+            out[4] = (kB_SH_C2[0] * xy) * dL_dRGB;
+            out[5] = (kB_SH_C2[1] * yz) * dL_dRGB;
+            out[6] = (kB_SH_C2[2] * (2.f * zz - xx - yy)) * dL_dRGB;
+            out[7] = (kB_SH_C2[3] * xz) * dL_dRGB;
+            out[8] = (kB_SH_C2[4] * (xx - yy)) * dL_dRGB;
+            written = 9;
+            if (deg > 2) {
+                out[9] = (kB_SH_C3[0] * y * (3.f * xx - yy)) * dL_dRGB;
+                out[10] = (kB_SH_C3[1] * xy * z) * dL_dRGB;
+                out[11] = (kB_SH_C3[2] * y * (4.f * zz - xx - yy)) * dL_dRGB;
+                out[12] = (kB_SH_C3[3] * z * (2.f * zz - 3.f * xx - 3.f * yy)) * dL_dRGB;
+                out[13] = (kB_SH_C3[4] * x * (4.f * zz - xx - yy)) * dL_dRGB;
+                out[14] = (kB_SH_C3[5] * z * (xx - yy)) * dL_dRGB;
+                out[15] = (kB_SH_C3[6] * x * (xx - 3.f * yy)) * dL_dRGB;
+                written = 16;
+            }
+        }
+    }
     for (int k = written; k < M; ++k) out[k] = mk(0, 0, 0);
     const f3 dL_ddir = mk(dot(dRGBdx, dL_dRGB), dot(dRGBdy, dL_dRGB), dot(dRGBdz, dL_dRGB));
     return dnormvdv(dir_orig, dL_ddir);
 }
 
+// Row stride (floats) of the shared-memory staging of SH rows: odd, so that the 256 threads of a block reading or
+// writing element k of their own row hit 32 different banks.
+__host__ __device__ inline int sh_stage_stride(int M) { return (3 * M) | 1; }
+
 __global__ void __launch_bounds__(kPreBlock, 4)
-preprocess_backward_kernel(BwdParams p, GeomState g, float* __restrict__ tau_partial) {
+preprocess_backward_kernel(BwdParams p, GeomState g, float* __restrict__ tau_partial, int stage_sh) {
     __shared__ float sV[16], sPm[16];
     __shared__ float s_tau[kPreBlock / 32][6];
+    extern __shared__ float s_sh[];      // [kPreBlock][sh_stage_stride(M)] when the SH rows are staged (stage_sh)
     if (threadIdx.x < 16) { sV[threadIdx.x] = p.viewmatrix[threadIdx.x]; sPm[threadIdx.x] = p.projmatrix[threadIdx.x]; }
+    // With more than one SH coefficient a thread's row is 12*M bytes: per-thread accesses would touch 32 different
+    // sectors per instruction (4 bytes used of each) on the way in AND on the way out. Instead the block copies its
+    // rows through shared memory, one warp per row with consecutive lanes on consecutive floats, and the per-Gaussian
+    // math reads coefficients from / writes gradient rows to its (bank-conflict-free) shared row in place.
+    const int row = 3 * p.M, stride = sh_stage_stride(p.M);
+    const int block_first = blockIdx.x * kPreBlock;
+    const int nrows = min(kPreBlock, p.P - block_first);
+    if (stage_sh) {
+        const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+        for (int r = warp; r < nrows; r += kPreBlock / 32) {
+            if (p.radii[block_first + r] <= 0) continue;                 // culled: its row is never read
+            const float* src = p.shs + (size_t)(block_first + r) * row;
+            for (int k = lane; k < row; k += 32) s_sh[r * stride + k] = src[k];
+        }
+    }
     __syncthreads();
     const int idx = blockIdx.x * kPreBlock + threadIdx.x;
     float tau[6] = {0, 0, 0, 0, 0, 0};
@@ -220,9 +248,10 @@ preprocess_backward_kernel(BwdParams p, GeomState g, float* __restrict__ tau_par
 
             // ---------------- SH (backward.cu:532-534) ----------------
             if (p.shs != nullptr && p.dL_dsh != nullptr) {
-                const f3 dm = sh_backward(p.D, p.M, p.shs + (size_t)idx * p.M * 3, m,
+                float* my_row = s_sh + threadIdx.x * stride;
+                const f3 dm = sh_backward(p.D, p.M, stage_sh ? my_row : p.shs + (size_t)idx * row, m,
                                           mk(p.campos[0], p.campos[1], p.campos[2]), g.clamped[idx],
-                                          mk(acc1.z, acc1.w, acc2.x), p.dL_dsh + (size_t)idx * p.M * 3);
+                                          mk(acc1.z, acc1.w, acc2.x), stage_sh ? my_row : p.dL_dsh + (size_t)idx * row);
                 dmean = dmean + dm;
                 tau[0] -= dm.x; tau[1] -= dm.y; tau[2] -= dm.z;
             }
@@ -261,8 +290,10 @@ preprocess_backward_kernel(BwdParams p, GeomState g, float* __restrict__ tau_par
                 reinterpret_cast<float4*>(p.dL_drot)[idx] = dq;
             }
         } else {
-            if (p.shs != nullptr && p.dL_dsh != nullptr)
-                for (int k = 0; k < p.M * 3; ++k) p.dL_dsh[(size_t)idx * p.M * 3 + k] = 0.0f;
+            if (p.shs != nullptr && p.dL_dsh != nullptr) {
+                float* dst = stage_sh ? s_sh + threadIdx.x * stride : p.dL_dsh + (size_t)idx * row;
+                for (int k = 0; k < row; ++k) dst[k] = 0.0f;
+            }
             if (p.scales != nullptr && p.dL_dscale != nullptr) {
                 p.dL_dscale[3 * idx] = 0.0f; p.dL_dscale[3 * idx + 1] = 0.0f; p.dL_dscale[3 * idx + 2] = 0.0f;
                 reinterpret_cast<float4*>(p.dL_drot)[idx] = make_float4(0, 0, 0, 0);
@@ -284,8 +315,15 @@ preprocess_backward_kernel(BwdParams p, GeomState g, float* __restrict__ tau_par
             for (int k = 0; k < 6; ++k) p.dL_dcov3D[6 * (size_t)idx + k] = dcov[k];
         }
     }
-    // camera-pose gradient: block-reduce the six components, one partial row per block
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (stage_sh) {                      // gradient rows: shared -> global, whole rows by consecutive lanes
+        __syncthreads();
+        for (int r = warp; r < nrows; r += kPreBlock / 32) {
+            float* dst = p.dL_dsh + (size_t)(block_first + r) * row;
+            for (int k = lane; k < row; k += 32) dst[k] = s_sh[r * stride + k];
+        }
+    }
+    // camera-pose gradient: block-reduce the six components, one partial row per block
 #pragma unroll
     for (int k = 0; k < 6; ++k) {
         float v = tau[k];
@@ -304,7 +342,19 @@ preprocess_backward_kernel(BwdParams p, GeomState g, float* __restrict__ tau_par
 
 void launch_preprocess_backward(const BwdParams& p, const GeomState& g, cudaStream_t s) {
     const int nblk = (p.P + kPreBlock - 1) / kPreBlock;
-    preprocess_backward_kernel<<<nblk, kPreBlock, 0, s>>>(p, g, p.dL_dtau);
+    // stage the SH rows through shared memory when they are longer than one coefficient (see the kernel)
+    const int stage_sh = (p.shs != nullptr && p.dL_dsh != nullptr && p.M > 1) ? 1 : 0;
+    const size_t smem = stage_sh ? sizeof(float) * (size_t)kPreBlock * sh_stage_stride(p.M) : 0;
+    if (smem > 48 * 1024) {
+        static bool raised[64] = {};     // opt in once per device to more than 48 KB of dynamic shared memory
+        int dev = 0;
+        cudaGetDevice(&dev);
+        if (dev >= 0 && dev < 64 && !raised[dev]) {
+            cudaFuncSetAttribute(preprocess_backward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
+            raised[dev] = true;
+        }
+    }
+    preprocess_backward_kernel<<<nblk, kPreBlock, smem, s>>>(p, g, p.dL_dtau, stage_sh);
 }
 
 }  // namespace splat
