@@ -43,7 +43,7 @@ __device__ __forceinline__ f3 dnormvdv(f3 v, f3 dv) {
 
 // SH backward (backward.cu:21-145): writes dL_dsh rows [0, M), returns dL/dmean through the view direction.
 // Everything that READS the coefficients (the direction derivatives dRGB/dx,y,z) comes before the first write of a
-// gradient row, so `dL_dsh_out` may be the same memory as `shs` (the shared-memory staging row of the caller).
+// gradient row. `dL_dsh_out` is either the global row or the caller's shared-memory staging row.
 __device__ f3 sh_backward(int deg, int M, const float* shs, f3 pos, f3 campos, uint8_t clamp_bits, f3 dL_dRGB,
                           float* dL_dsh_out) {
     const f3 dir_orig = mk(pos.x - campos.x, pos.y - campos.y, pos.z - campos.z);
@@ -122,21 +122,14 @@ preprocess_backward_kernel(BwdParams p, GeomState g, float* __restrict__ tau_par
     __shared__ float s_tau[kPreBlock / 32][6];
     extern __shared__ float s_sh[];      // [kPreBlock][sh_stage_stride(M)] when the SH rows are staged (stage_sh)
     if (threadIdx.x < 16) { sV[threadIdx.x] = p.viewmatrix[threadIdx.x]; sPm[threadIdx.x] = p.projmatrix[threadIdx.x]; }
-    // With more than one SH coefficient a thread's row is 12*M bytes: per-thread accesses would touch 32 different
-    // sectors per instruction (4 bytes used of each) on the way in AND on the way out. Instead the block copies its
-    // rows through shared memory, one warp per row with consecutive lanes on consecutive floats, and the per-Gaussian
-    // math reads coefficients from / writes gradient rows to its (bank-conflict-free) shared row in place.
+    // With more than one SH coefficient a thread's gradient row is 12*M bytes: per-thread stores would touch 32
+    // different sectors per instruction (4 bytes of each). Instead every thread writes its row into shared memory
+    // (odd row stride: no bank conflicts) and the block copies its rows out as one contiguous range of float4.
+    // (Staging the coefficient READS the same way was measured and is slower: the per-thread loads overlap with the
+    // covariance math, a separate load phase does not.)
     const int row = 3 * p.M, stride = sh_stage_stride(p.M);
     const int block_first = blockIdx.x * kPreBlock;
     const int nrows = min(kPreBlock, p.P - block_first);
-    if (stage_sh) {
-        const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-        for (int r = warp; r < nrows; r += kPreBlock / 32) {
-            if (p.radii[block_first + r] <= 0) continue;                 // culled: its row is never read
-            const float* src = p.shs + (size_t)(block_first + r) * row;
-            for (int k = lane; k < row; k += 32) s_sh[r * stride + k] = src[k];
-        }
-    }
     __syncthreads();
     const int idx = blockIdx.x * kPreBlock + threadIdx.x;
     float tau[6] = {0, 0, 0, 0, 0, 0};
@@ -249,7 +242,7 @@ preprocess_backward_kernel(BwdParams p, GeomState g, float* __restrict__ tau_par
             // ---------------- SH (backward.cu:532-534) ----------------
             if (p.shs != nullptr && p.dL_dsh != nullptr) {
                 float* my_row = s_sh + threadIdx.x * stride;
-                const f3 dm = sh_backward(p.D, p.M, stage_sh ? my_row : p.shs + (size_t)idx * row, m,
+                const f3 dm = sh_backward(p.D, p.M, p.shs + (size_t)idx * row, m,
                                           mk(p.campos[0], p.campos[1], p.campos[2]), g.clamped[idx],
                                           mk(acc1.z, acc1.w, acc2.x), stage_sh ? my_row : p.dL_dsh + (size_t)idx * row);
                 dmean = dmean + dm;
@@ -316,11 +309,19 @@ preprocess_backward_kernel(BwdParams p, GeomState g, float* __restrict__ tau_par
         }
     }
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    if (stage_sh) {                      // gradient rows: shared -> global, whole rows by consecutive lanes
+    if (stage_sh) {                      // gradient rows: shared -> global; the block's rows are one contiguous range
         __syncthreads();
-        for (int r = warp; r < nrows; r += kPreBlock / 32) {
-            float* dst = p.dL_dsh + (size_t)(block_first + r) * row;
-            for (int k = lane; k < row; k += 32) dst[k] = s_sh[r * stride + k];
+        float* dst = p.dL_dsh + (size_t)block_first * row;
+        if ((row & 3) == 0 && (reinterpret_cast<uintptr_t>(dst) & 15u) == 0) {
+            const int q = row >> 2, total = nrows * q;          // float4 chunks per row / in the block
+            for (int f = threadIdx.x; f < total; f += kPreBlock) {
+                const int r = f / q, c = f - r * q;
+                const float* src = s_sh + r * stride + 4 * c;
+                reinterpret_cast<float4*>(dst)[f] = make_float4(src[0], src[1], src[2], src[3]);
+            }
+        } else {
+            for (int r = warp; r < nrows; r += kPreBlock / 32)
+                for (int k = lane; k < row; k += 32) dst[(size_t)r * row + k] = s_sh[r * stride + k];
         }
     }
     // camera-pose gradient: block-reduce the six components, one partial row per block
