@@ -18,23 +18,44 @@ __device__ const float kSH_C3[7] = {-0.5900435899266435f, 2.890611442640554f, -0
                                     -0.5900435899266435f};
 
 // SH -> RGB with +0.5 and clamp at 0 (DGR forward.cu:22-73). Colours only need 1e-5, so plain float code.
+// A row is 12*M bytes; when it is 16-byte aligned (M a multiple of 4, i.e. the SH degree 1 and 3 layouts) it is read
+// with 128-bit loads, a degree at a time — a quarter of the load instructions and of the L1 sector traffic of 4-byte
+// loads, which is what bounded this kernel at SH degree 3.
+template <bool kHigherDegrees>
 __device__ __forceinline__ float3 sh_to_rgb(int deg, int M, const float* __restrict__ sh, float3 pos, float3 campos,
                                             uint8_t& clamp_bits) {
     float3 dir = make_float3(pos.x - campos.x, pos.y - campos.y, pos.z - campos.z);
     const float len = sqrtf(dir.x * dir.x + dir.y * dir.y + dir.z * dir.z);
     dir.x /= len; dir.y /= len; dir.z /= len;
-    const float3* c = reinterpret_cast<const float3*>(sh);
-    (void)M;
-    float3 r = make_float3(kSH_C0 * c[0].x, kSH_C0 * c[0].y, kSH_C0 * c[0].z);
-    if (deg > 0) {
+    const bool vec = ((M & 3) == 0) && ((reinterpret_cast<uintptr_t>(sh) & 15u) == 0);
+    const float4* sh4 = reinterpret_cast<const float4*>(sh);
+    float f[48];
+#define SH_LOAD(first4, count4)                                                        \
+    _Pragma("unroll") for (int i__ = (first4); i__ < (first4) + (count4); ++i__) {     \
+        if (vec) {                                                                     \
+            const float4 v__ = __ldg(sh4 + i__);                                       \
+            f[4 * i__] = v__.x; f[4 * i__ + 1] = v__.y; f[4 * i__ + 2] = v__.z; f[4 * i__ + 3] = v__.w; \
+        } else {                                                                       \
+            _Pragma("unroll") for (int j__ = 0; j__ < 4; ++j__)                        \
+                f[4 * i__ + j__] = (4 * i__ + j__ < 3 * M) ? sh[4 * i__ + j__] : 0.0f; \
+        }                                                                              \
+    }
+#define SH_ACC(w, k) { const float w__ = (w); r.x += w__ * f[3 * (k)]; r.y += w__ * f[3 * (k) + 1]; r.z += w__ * f[3 * (k) + 2]; }
+    float3 r;
+    if (!kHigherDegrees || deg == 0) {   // 3 floats: not worth a 16-byte load, and M may be 1
+        r = make_float3(kSH_C0 * sh[0], kSH_C0 * sh[1], kSH_C0 * sh[2]);
+    } else {
+        SH_LOAD(0, 3)                    // coefficients 0..3
+        r = make_float3(kSH_C0 * f[0], kSH_C0 * f[1], kSH_C0 * f[2]);
         const float x = dir.x, y = dir.y, z = dir.z;
-#define SH_ACC(w, k) { const float w__ = (w); r.x += w__ * c[k].x; r.y += w__ * c[k].y; r.z += w__ * c[k].z; }
         SH_ACC(-kSH_C1 * y, 1) SH_ACC(kSH_C1 * z, 2) SH_ACC(-kSH_C1 * x, 3)
         if (deg > 1) {
+            SH_LOAD(3, 4)                // floats 12..27: coefficients 4..8 (+ the first float of 9)
             const float xx = x * x, yy = y * y, zz = z * z, xy = x * y, yz = y * z, xz = x * z;
             SH_ACC(kSH_C2[0] * xy, 4) SH_ACC(kSH_C2[1] * yz, 5) SH_ACC(kSH_C2[2] * (2.0f * zz - xx - yy), 6)
             SH_ACC(kSH_C2[3] * xz, 7) SH_ACC(kSH_C2[4] * (xx - yy), 8)
             if (deg > 2) {
+                SH_LOAD(7, 5)            // floats 28..47: coefficients 9..15
                 SH_ACC(kSH_C3[0] * y * (3.0f * xx - yy), 9) SH_ACC(kSH_C3[1] * xy * z, 10)
                 SH_ACC(kSH_C3[2] * y * (4.0f * zz - xx - yy), 11)
                 SH_ACC(kSH_C3[3] * z * (2.0f * zz - 3.0f * xx - 3.0f * yy), 12)
@@ -42,13 +63,17 @@ __device__ __forceinline__ float3 sh_to_rgb(int deg, int M, const float* __restr
                 SH_ACC(kSH_C3[6] * x * (xx - 3.0f * yy), 15)
             }
         }
-#undef SH_ACC
     }
+#undef SH_ACC
+#undef SH_LOAD
     r.x += 0.5f; r.y += 0.5f; r.z += 0.5f;
     clamp_bits = (r.x < 0.0f ? 1 : 0) | (r.y < 0.0f ? 2 : 0) | (r.z < 0.0f ? 4 : 0);
     return make_float3(fmaxf(r.x, 0.0f), fmaxf(r.y, 0.0f), fmaxf(r.z, 0.0f));
 }
 
+// kHigherDegrees = false is the SH degree 0 build (Splat-SLAM's own setting): without the higher-degree code it needs
+// fewer registers and keeps its occupancy.
+template <bool kHigherDegrees>
 __global__ void __launch_bounds__(kPreBlock)
 preprocess_forward_kernel(int P, int D, int M,
                           const float* __restrict__ means3D, const float* __restrict__ scales, float scale_modifier,
@@ -113,7 +138,7 @@ preprocess_forward_kernel(int P, int D, int M,
             float3 c;
             if (colors_precomp == nullptr) {
                 uint8_t cb;
-                c = sh_to_rgb(D, M, shs + (size_t)idx * M * 3, make_float3(px, py, pz),
+                c = sh_to_rgb<kHigherDegrees>(D, M, shs + (size_t)idx * M * 3, make_float3(px, py, pz),
                               make_float3(campos[0], campos[1], campos[2]), cb);
                 g.rgb[3 * idx] = c.x; g.rgb[3 * idx + 1] = c.y; g.rgb[3 * idx + 2] = c.z;
                 g.clamped[idx] = cb;
@@ -166,7 +191,8 @@ __global__ void mark_visible_kernel(int P, const float* __restrict__ means3D, co
 
 void launch_preprocess_forward(const FwdParams& p, const GeomState& g, cudaStream_t s) {
     const int nblk = (p.P + kPreBlock - 1) / kPreBlock;
-    preprocess_forward_kernel<<<nblk, kPreBlock, 0, s>>>(
+    auto kernel = (p.shs != nullptr && p.D > 0) ? preprocess_forward_kernel<true> : preprocess_forward_kernel<false>;
+    kernel<<<nblk, kPreBlock, 0, s>>>(
         p.P, p.D, p.M, p.means3D, p.scales, p.scale_modifier, p.rotations, p.opacities, p.shs, p.cov3D_precomp,
         p.colors_precomp, p.viewmatrix, p.projmatrix, p.campos, p.W, p.H, p.tanfovx, p.tanfovy, p.focal_x, p.focal_y,
         p.grid_x, p.grid_y, p.prefiltered, p.radii, p.n_touched, g);
