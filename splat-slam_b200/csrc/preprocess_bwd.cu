@@ -44,12 +44,28 @@ __device__ __forceinline__ f3 dnormvdv(f3 v, f3 dv) {
 // SH backward (backward.cu:21-145): writes dL_dsh rows [0, M), returns dL/dmean through the view direction.
 // Everything that READS the coefficients (the direction derivatives dRGB/dx,y,z) comes before the first write of a
 // gradient row. `dL_dsh_out` is either the global row or the caller's shared-memory staging row.
+template <bool kHigherDegrees>
 __device__ f3 sh_backward(int deg, int M, const float* shs, f3 pos, f3 campos, uint8_t clamp_bits, f3 dL_dRGB,
                           float* dL_dsh_out) {
+    if (!kHigherDegrees) deg = 0;        // the SH degree 0 build carries none of the higher-degree code
     const f3 dir_orig = mk(pos.x - campos.x, pos.y - campos.y, pos.z - campos.z);
     const float inv_len = 1.0f / sqrtf(dot(dir_orig, dir_orig));
     const float x = dir_orig.x * inv_len, y = dir_orig.y * inv_len, z = dir_orig.z * inv_len;
-    const f3* sh = reinterpret_cast<const f3*>(shs);
+    // coefficient row read with 128-bit loads when it is 16-byte aligned (M a multiple of 4), a degree at a time
+    const bool vec = ((M & 3) == 0) && ((reinterpret_cast<uintptr_t>(shs) & 15u) == 0);
+    const float4* sh4 = reinterpret_cast<const float4*>(shs);
+    float f[48];
+#define SH_LOAD(first4, count4)                                                        \
+    _Pragma("unroll") for (int i__ = (first4); i__ < (first4) + (count4); ++i__) {     \
+        if (vec) {                                                                     \
+            const float4 v__ = __ldg(sh4 + i__);                                       \
+            f[4 * i__] = v__.x; f[4 * i__ + 1] = v__.y; f[4 * i__ + 2] = v__.z; f[4 * i__ + 3] = v__.w; \
+        } else {                                                                       \
+            _Pragma("unroll") for (int j__ = 0; j__ < 4; ++j__)                        \
+                f[4 * i__ + j__] = (4 * i__ + j__ < 3 * M) ? shs[4 * i__ + j__] : 0.0f; \
+        }                                                                              \
+    }
+#define SHC(k) mk(f[3 * (k)], f[3 * (k) + 1], f[3 * (k) + 2])
     f3* out = reinterpret_cast<f3*>(dL_dsh_out);
     if (clamp_bits & 1) dL_dRGB.x = 0.0f;
     if (clamp_bits & 2) dL_dRGB.y = 0.0f;
@@ -57,27 +73,30 @@ __device__ f3 sh_backward(int deg, int M, const float* shs, f3 pos, f3 campos, u
     const float xx = x * x, yy = y * y, zz = z * z, xy = x * y, yz = y * z, xz = x * z;
     f3 dRGBdx = mk(0, 0, 0), dRGBdy = mk(0, 0, 0), dRGBdz = mk(0, 0, 0);
     if (deg > 0) {
-        dRGBdx = (-kB_SH_C1) * sh[3];
-        dRGBdy = (-kB_SH_C1) * sh[1];
-        dRGBdz = kB_SH_C1 * sh[2];
+        SH_LOAD(0, 3)
+        dRGBdx = (-kB_SH_C1) * SHC(3);
+        dRGBdy = (-kB_SH_C1) * SHC(1);
+        dRGBdz = kB_SH_C1 * SHC(2);
         if (deg > 1) {
-            dRGBdx = dRGBdx + (kB_SH_C2[0] * y) * sh[4] + (kB_SH_C2[2] * 2.f * -x) * sh[6] + (kB_SH_C2[3] * z) * sh[7] +
-                     (kB_SH_C2[4] * 2.f * x) * sh[8];
-            dRGBdy = dRGBdy + (kB_SH_C2[0] * x) * sh[4] + (kB_SH_C2[1] * z) * sh[5] + (kB_SH_C2[2] * 2.f * -y) * sh[6] +
-                     (kB_SH_C2[4] * 2.f * -y) * sh[8];
-            dRGBdz = dRGBdz + (kB_SH_C2[1] * y) * sh[5] + (kB_SH_C2[2] * 2.f * 2.f * z) * sh[6] + (kB_SH_C2[3] * x) * sh[7];
+            SH_LOAD(3, 4)
+            dRGBdx = dRGBdx + (kB_SH_C2[0] * y) * SHC(4) + (kB_SH_C2[2] * 2.f * -x) * SHC(6) + (kB_SH_C2[3] * z) * SHC(7) +
+                     (kB_SH_C2[4] * 2.f * x) * SHC(8);
+            dRGBdy = dRGBdy + (kB_SH_C2[0] * x) * SHC(4) + (kB_SH_C2[1] * z) * SHC(5) + (kB_SH_C2[2] * 2.f * -y) * SHC(6) +
+                     (kB_SH_C2[4] * 2.f * -y) * SHC(8);
+            dRGBdz = dRGBdz + (kB_SH_C2[1] * y) * SHC(5) + (kB_SH_C2[2] * 2.f * 2.f * z) * SHC(6) + (kB_SH_C2[3] * x) * SHC(7);
             if (deg > 2) {
-                dRGBdx = dRGBdx + (kB_SH_C3[0] * 3.f * 2.f * xy) * sh[9] + (kB_SH_C3[1] * yz) * sh[10] +
-                         (kB_SH_C3[2] * -2.f * xy) * sh[11] + (kB_SH_C3[3] * -3.f * 2.f * xz) * sh[12] +
-                         (kB_SH_C3[4] * (-3.f * xx + 4.f * zz - yy)) * sh[13] + (kB_SH_C3[5] * 2.f * xz) * sh[14] +
-                         (kB_SH_C3[6] * 3.f * (xx - yy)) * sh[15];
-                dRGBdy = dRGBdy + (kB_SH_C3[0] * 3.f * (xx - yy)) * sh[9] + (kB_SH_C3[1] * xz) * sh[10] +
-                         (kB_SH_C3[2] * (-3.f * yy + 4.f * zz - xx)) * sh[11] + (kB_SH_C3[3] * -3.f * 2.f * yz) * sh[12] +
-                         (kB_SH_C3[4] * -2.f * xy) * sh[13] + (kB_SH_C3[5] * -2.f * yz) * sh[14] +
-                         (kB_SH_C3[6] * -3.f * 2.f * xy) * sh[15];
-                dRGBdz = dRGBdz + (kB_SH_C3[1] * xy) * sh[10] + (kB_SH_C3[2] * 4.f * 2.f * yz) * sh[11] +
-                         (kB_SH_C3[3] * 3.f * (2.f * zz - xx - yy)) * sh[12] + (kB_SH_C3[4] * 4.f * 2.f * xz) * sh[13] +
-                         (kB_SH_C3[5] * (xx - yy)) * sh[14];
+                SH_LOAD(7, 5)
+                dRGBdx = dRGBdx + (kB_SH_C3[0] * 3.f * 2.f * xy) * SHC(9) + (kB_SH_C3[1] * yz) * SHC(10) +
+                         (kB_SH_C3[2] * -2.f * xy) * SHC(11) + (kB_SH_C3[3] * -3.f * 2.f * xz) * SHC(12) +
+                         (kB_SH_C3[4] * (-3.f * xx + 4.f * zz - yy)) * SHC(13) + (kB_SH_C3[5] * 2.f * xz) * SHC(14) +
+                         (kB_SH_C3[6] * 3.f * (xx - yy)) * SHC(15);
+                dRGBdy = dRGBdy + (kB_SH_C3[0] * 3.f * (xx - yy)) * SHC(9) + (kB_SH_C3[1] * xz) * SHC(10) +
+                         (kB_SH_C3[2] * (-3.f * yy + 4.f * zz - xx)) * SHC(11) + (kB_SH_C3[3] * -3.f * 2.f * yz) * SHC(12) +
+                         (kB_SH_C3[4] * -2.f * xy) * SHC(13) + (kB_SH_C3[5] * -2.f * yz) * SHC(14) +
+                         (kB_SH_C3[6] * -3.f * 2.f * xy) * SHC(15);
+                dRGBdz = dRGBdz + (kB_SH_C3[1] * xy) * SHC(10) + (kB_SH_C3[2] * 4.f * 2.f * yz) * SHC(11) +
+                         (kB_SH_C3[3] * 3.f * (2.f * zz - xx - yy)) * SHC(12) + (kB_SH_C3[4] * 4.f * 2.f * xz) * SHC(13) +
+                         (kB_SH_C3[5] * (xx - yy)) * SHC(14);
             }
         }
     }
@@ -110,12 +129,15 @@ __device__ f3 sh_backward(int deg, int M, const float* shs, f3 pos, f3 campos, u
     for (int k = written; k < M; ++k) out[k] = mk(0, 0, 0);
     const f3 dL_ddir = mk(dot(dRGBdx, dL_dRGB), dot(dRGBdy, dL_dRGB), dot(dRGBdz, dL_dRGB));
     return dnormvdv(dir_orig, dL_ddir);
+#undef SHC
+#undef SH_LOAD
 }
 
 // Row stride (floats) of the shared-memory staging of SH rows: odd, so that the 256 threads of a block reading or
 // writing element k of their own row hit 32 different banks.
 __host__ __device__ inline int sh_stage_stride(int M) { return (3 * M) | 1; }
 
+template <bool kHigherDegrees>
 __global__ void __launch_bounds__(kPreBlock, 4)
 preprocess_backward_kernel(BwdParams p, GeomState g, float* __restrict__ tau_partial, int stage_sh) {
     __shared__ float sV[16], sPm[16];
@@ -242,7 +264,7 @@ preprocess_backward_kernel(BwdParams p, GeomState g, float* __restrict__ tau_par
             // ---------------- SH (backward.cu:532-534) ----------------
             if (p.shs != nullptr && p.dL_dsh != nullptr) {
                 float* my_row = s_sh + threadIdx.x * stride;
-                const f3 dm = sh_backward(p.D, p.M, p.shs + (size_t)idx * row, m,
+                const f3 dm = sh_backward<kHigherDegrees>(p.D, p.M, p.shs + (size_t)idx * row, m,
                                           mk(p.campos[0], p.campos[1], p.campos[2]), g.clamped[idx],
                                           mk(acc1.z, acc1.w, acc2.x), stage_sh ? my_row : p.dL_dsh + (size_t)idx * row);
                 dmean = dmean + dm;
@@ -351,11 +373,15 @@ void launch_preprocess_backward(const BwdParams& p, const GeomState& g, cudaStre
         int dev = 0;
         cudaGetDevice(&dev);
         if (dev >= 0 && dev < 64 && !raised[dev]) {
-            cudaFuncSetAttribute(preprocess_backward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
+            cudaFuncSetAttribute(preprocess_backward_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
+            cudaFuncSetAttribute(preprocess_backward_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
             raised[dev] = true;
         }
     }
-    preprocess_backward_kernel<<<nblk, kPreBlock, smem, s>>>(p, g, p.dL_dtau, stage_sh);
+    if (p.shs != nullptr && p.D > 0)
+        preprocess_backward_kernel<true><<<nblk, kPreBlock, smem, s>>>(p, g, p.dL_dtau, stage_sh);
+    else
+        preprocess_backward_kernel<false><<<nblk, kPreBlock, smem, s>>>(p, g, p.dL_dtau, stage_sh);
 }
 
 }  // namespace splat
