@@ -98,6 +98,7 @@ render_forward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ranges
     __shared__ __align__(8) uint64_t s_bar[2];
     __shared__ int s_cnt[2][kBatch];
     __shared__ uint8_t s_list[SPLAT_TILE_PIXELS / 32][kBatch];
+    __shared__ uint32_t s_tv[SPLAT_TILE_PIXELS / 32][kBatch];
 
     const int tile = blockIdx.x;
     const int tile_x = tile % grid_x, tile_y = tile / grid_x;
@@ -137,7 +138,8 @@ render_forward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ranges
         mbar_wait(&s_bar[stage], (uint32_t)((b >> 1) & 1));
         const float4* rec = &s_rec[stage][0];
         const int n_live = __all_sync(0xffffffffu, done) ? 0 : bin_batch_for_warp(rec, cnt, patch, s_list[warp], lane);
-        for (int k = 0; k < n_live; ++k) {
+        int k = 0;
+        for (; k < n_live; ++k) {
             // survivors of the binning almost always touch some lane, so everything up to the blend is evaluated
             // unconditionally and a single ballot per instance serves both the blend and the n_touched count
             const int j = s_list[warp][k];
@@ -160,10 +162,16 @@ render_forward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ranges
                 T = test_T;
                 last_contributor = (uint32_t)(b * kBatch + j + 1);
             }
-            // n_touched: pixels that blended this Gaussian while still > 50 % transparent (forward.cu:368-370)
+            // n_touched: pixels that blended this Gaussian while still > 50 % transparent (forward.cu:368-370). The vote
+            // is only parked here; counting and the shared-memory add are done for 32 instances at a time below.
             const uint32_t tv = __ballot_sync(0xffffffffu, act && test_T > 0.5f);
-            if (tv != 0u && lane == 0) atomicAdd(&s_cnt[stage][j], __popc(tv));
-            if (__all_sync(0xffffffffu, done)) break;
+            if (lane == 0) s_tv[warp][k] = tv;
+            if (__all_sync(0xffffffffu, done)) { ++k; break; }
+        }
+        __syncwarp();
+        for (int i = (int)lane; i < k; i += 32) {
+            const int c = __popc(s_tv[warp][i]);
+            if (c) atomicAdd(&s_cnt[stage][s_list[warp][i]], c);
         }
         __syncthreads();   // every warp is done with this stage
         if (threadIdx.x < cnt) {
