@@ -77,3 +77,14 @@ def test_window_step_world2_matches_single_process(tmp_path, n_views):
     # grads are views into the flat buffer, in PARAM_ORDER
     assert params["means3D"].grad.data_ptr() == flat.flat.data_ptr()
     assert flat.flat.numel() == sum(p.numel() for p in params.values())
+
+
+def test_view_streams_without_side_streams_is_a_no_op():
+    """n <= 1: no CUDA stream is created, fork/join do nothing, view() is a null context (CPU-safe)."""
+    from diff_gaussian_rasterization.window import ViewStreams
+    vs = ViewStreams("cpu", 1)
+    assert len(vs) == 0
+    vs.fork()
+    with vs.view(3):
+        pass
+    vs.join()
