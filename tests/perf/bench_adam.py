@@ -1,13 +1,13 @@
 """Times the fused Adam step against torch.optim.Adam (what the reference steps, gaussian_model.py:302) on the six
 Gaussian parameter groups at 1 M Gaussians, SH degree 0 (14 M parameters).
-    gpurun -- 'python scripts/bench_adam.py'
+    gpurun -- 'python tests/perf/bench_adam.py'
 """
 import os
 import sys
 
 import torch
 
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, os.path.join(ROOT, "splat-slam_b200"))
 from diff_gaussian_rasterization.adam import GaussianAdam  # noqa: E402
 

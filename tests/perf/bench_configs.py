@@ -1,15 +1,15 @@
-"""BASELINE.json configs 1 and 5 (the bench covers config 3/4's shape, scripts/bench_tracking.py config 2):
+"""BASELINE.json configs 1 and 5 (the bench covers config 3/4's shape, tests/perf/bench_tracking.py config 2):
   config 1: Replica 1200x680, 500 k Gaussians, SH degree 0, fwd+bwd with pose gradients, one view per iteration
   config 5: ScanNet 1296x968 final colour refinement, 3 M Gaussians, SH degree 3, one view per iteration
 Times this library and the compiled reference extension on the same inputs (single stream, one view at a time).
-    gpurun -- 'python scripts/bench_configs.py'
+    gpurun -- 'python tests/perf/bench_configs.py'
 """
 import os
 import sys
 
 import torch
 
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, os.path.join(ROOT, "splat-slam_b200"))
 sys.path.insert(0, os.path.join(ROOT, "oracle", "_ref"))
 import diff_gaussian_rasterization as ours  # noqa: E402

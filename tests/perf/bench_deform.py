@@ -1,13 +1,13 @@
 """Times the fused map deformation against the reference's per-keyframe torch sequence (oracle.deform on the GPU = the
 same ops src/mapper.py:154-255 issues, without the optimizer re-registration) for 100 keyframes over 1 M Gaussians.
-    gpurun -- 'python scripts/bench_deform.py'
+    gpurun -- 'python tests/perf/bench_deform.py'
 """
 import os
 import sys
 
 import torch
 
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "splat-slam_b200"))
 from diff_gaussian_rasterization.deform import deform_points_  # noqa: E402

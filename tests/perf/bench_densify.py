@@ -1,6 +1,6 @@
 """Times the fused densification bookkeeping against the reference's per-view torch indexing loop
 (src/mapper.py:519-529 + gaussian_model.py:738-742, run here on the GPU as the reference runs it) for 12 views.
-    gpurun -- 'python scripts/bench_densify.py'
+    gpurun -- 'python tests/perf/bench_densify.py'
 """
 import os
 import sys
@@ -8,7 +8,7 @@ import types
 
 import torch
 
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "splat-slam_b200"))
 from diff_gaussian_rasterization.densify import add_densification_stats_window  # noqa: E402

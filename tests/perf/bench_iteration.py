@@ -6,7 +6,7 @@
   ours      : fused activations once per iteration, this library's rasterizer with the views on three streams, fused
               mapping loss, per-view backward, fused densification stats / visibility, GaussianAdam for both optimizers.
 
-    gpurun -- 'python scripts/bench_iteration.py'          # prints ms per iteration for each arm
+    gpurun -- 'python tests/perf/bench_iteration.py'          # prints ms per iteration for each arm
 """
 import os
 import sys
@@ -14,7 +14,7 @@ import types
 
 import torch
 
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "splat-slam_b200"))
 sys.path.insert(0, os.path.join(ROOT, "oracle", "_ref"))

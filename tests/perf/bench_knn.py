@@ -1,12 +1,12 @@
 """Times distCUDA2 (ours) against the compiled reference simple-knn (oracle/_ref/ref_simple_knn) on a B200.
-    gpurun -- 'python scripts/bench_knn.py'
+    gpurun -- 'python tests/perf/bench_knn.py'
 """
 import os
 import sys
 
 import torch
 
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "splat-slam_b200"))
 sys.path.insert(0, os.path.join(ROOT, "oracle", "_ref"))

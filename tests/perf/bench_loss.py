@@ -1,13 +1,13 @@
 """Times the fused mapping-loss kernel (forward + backward) against the reference's chain of torch ops
 (oracle.mapping_loss on the GPU = the same ops slam_utils.py:71-105 issues) at the Replica frame size.
-    gpurun -- 'python scripts/bench_loss.py'
+    gpurun -- 'python tests/perf/bench_loss.py'
 """
 import os
 import sys
 
 import torch
 
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "splat-slam_b200"))
 from diff_gaussian_rasterization.mapping_loss import fused_mapping_loss  # noqa: E402

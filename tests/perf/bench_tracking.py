@@ -1,6 +1,6 @@
 """BASELINE.json config 3: TUM-RGBD-shape 640x480 tracking, pose-only (theta, rho) gradients, 200k Gaussians,
 100 iterations. Times this library and the compiled reference extension on the same inputs.
-    gpurun -- 'python scripts/bench_tracking.py'
+    gpurun -- 'python tests/perf/bench_tracking.py'
 """
 import os
 import sys
@@ -8,7 +8,7 @@ import time
 
 import torch
 
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, os.path.join(ROOT, "splat-slam_b200"))
 sys.path.insert(0, os.path.join(ROOT, "oracle", "_ref"))
 import diff_gaussian_rasterization as ours  # noqa: E402

@@ -1,6 +1,6 @@
 """Runs each of the kernels around the rasterizer once at bench size, for an ncu capture:
     ncu --set full --clock-control none --import-source on -k regex:'adam_step|mapping_loss|densify_stats|knn_search|deform_points|activations_' \
-        -o gpurun_out/r01_f python scripts/ncu_f_kernels.py
+        -o gpurun_out/r01_f python tests/perf/ncu_f_kernels.py
 """
 import os
 import sys
@@ -8,7 +8,7 @@ import types
 
 import torch
 
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "splat-slam_b200"))
 from diff_gaussian_rasterization.activations import fused_activations  # noqa: E402
