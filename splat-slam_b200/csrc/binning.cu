@@ -153,7 +153,7 @@ void launch_duplicate_with_keys(int P, int grid_x, int grid_y, const int* radii,
 // ---- tile ranges + render records --------------------------------------------------------------------
 // One thread per sorted instance: detects tile boundaries (identifyTileRanges), materialises the reference's 64-bit
 // key (tile << 32 | depth bits) for inspection, and copies the instance's 48-byte per-Gaussian record
-// {x, y, conic.x, conic.y | conic.z, opacity, depth, id | r, g, b, footprint box} (written by
+// {x, y, id, footprint box | conic.x, conic.y, conic.z, opacity | r, g, b, depth} (written by
 // preprocess_forward_kernel) into sorted order, so the render kernels stream contiguous records with bulk async
 // copies instead of four dependent gathers per instance.
 __global__ void __launch_bounds__(256)
@@ -179,11 +179,11 @@ ranges_and_records_kernel(int R, const uint32_t* __restrict__ tkeys, const uint3
         if (i == R - 1) ranges[tile].y = R;
         // gather the Gaussian's 48-byte record (three 16-byte loads from one contiguous chunk)
         const float4* src = gauss_rec + 3 * (size_t)point_list[i];
-        const float4 r1 = src[1];
+        const float4 r2 = src[2];
         s_t[warp][lane * 3 + 0] = src[0];
-        s_t[warp][lane * 3 + 1] = r1;
-        s_t[warp][lane * 3 + 2] = src[2];
-        keys64[i] = ((uint64_t)tile << 32) | (uint64_t)__float_as_uint(r1.z);
+        s_t[warp][lane * 3 + 1] = src[1];
+        s_t[warp][lane * 3 + 2] = r2;
+        keys64[i] = ((uint64_t)tile << 32) | (uint64_t)__float_as_uint(r2.w);
     }
     __syncwarp();
     // the warp's 32 records are contiguous in the output: write them as three fully coalesced 512-byte rows

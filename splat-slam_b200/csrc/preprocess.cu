@@ -149,10 +149,13 @@ preprocess_forward_kernel(int P, int D, int M,
             g.means2D[idx] = pim;
             g.conic_opacity[idx] = con_o;
             // everything the render kernels need for this Gaussian, as one 48-byte record
-            g.rec[3 * (size_t)idx + 0] = make_float4(pim.x, pim.y, con_o.x, con_o.y);
-            g.rec[3 * (size_t)idx + 1] = make_float4(con_o.z, con_o.w, tz, __int_as_float(idx));
-            g.rec[3 * (size_t)idx + 2] = make_float4(
-                c.x, c.y, c.z, __uint_as_float(footprint_half_extents(con_o.x, con_o.y, con_o.z, con_o.w)));
+            // {x, y, id, footprint box | conic.x, conic.y, conic.z, opacity | r, g, b, depth}: the first quarter is all the
+            // per-warp binning reads, the first two decide whether a pixel blends, the last is only read if one does
+            g.rec[3 * (size_t)idx + 0] = make_float4(
+                pim.x, pim.y, __int_as_float(idx),
+                __uint_as_float(footprint_half_extents(con_o.x, con_o.y, con_o.z, con_o.w)));
+            g.rec[3 * (size_t)idx + 1] = con_o;
+            g.rec[3 * (size_t)idx + 2] = make_float4(c.x, c.y, c.z, tz);
             radius_out = my_radius;
             tiles = area;
             tz_out = tz;

@@ -3,11 +3,12 @@
 //
 // B200 design: one CTA per 16x16 tile (tile ids/ranges stay bit-compatible with the reference). Each warp owns
 // an 8x4 pixel patch so whole-warp rejection of a Gaussian is likely. Per-instance 48-byte records (built in
-// sorted order by ranges_and_records_kernel) are streamed into a two-stage shared-memory ring with
-// cp.async.bulk (TMA 1-D bulk copy, SASS UBLKCP) completing on an mbarrier; the consumer loop reads them with
-// broadcast LDS.128. The backward reduces the 10 per-Gaussian gradient terms across the warp with a
-// recursive-halving shuffle tree (12 SHFL instead of 50) and issues one RED per term per warp.
+// sorted order by ranges_and_records_kernel) are streamed into a shared-memory ring with cp.async.bulk (TMA 1-D
+// bulk copy, SASS UBLKCP) completing on an mbarrier; the consumer loops read them with broadcast LDS.128.
+// The backward takes the per-Gaussian sums in a transposed second phase (lane = Gaussian) instead of a cross-lane
+// reduction, and its warps walk the ring independently (no block barrier per batch); see render_backward_kernel.
 #include <cuda_fp16.h>
+#include <cstdlib>
 #include "common.cuh"
 #include "kernels.h"
 
@@ -63,17 +64,18 @@ __device__ __forceinline__ float4 patch_of_warp(int tile_x, int tile_y) {
 // compacted, in order, into `list`. A (warp, instance) pair that cannot reach alpha >= 1/255 anywhere in the patch
 // then costs ~0.5 instructions instead of a full power/exp evaluation by all 32 lanes. Comparisons are written so
 // that NaN coordinates count as "inside" (the reference would still evaluate them). Returns the survivor count.
+template <int kRecords = kBatch>
 __device__ __forceinline__ int bin_batch_for_warp(const float4* rec, int cnt, float4 patch, uint8_t* list,
                                                   uint32_t lane) {
     int n = 0;
     const uint32_t lt = (1u << lane) - 1u;
 #pragma unroll
-    for (int r = 0; r < kBatch / 32; ++r) {
+    for (int r = 0; r < kRecords / 32; ++r) {
         const int j = r * 32 + (int)lane;
         bool live = false;
         if (j < cnt) {
-            const float4 r0 = rec[3 * j];
-            const uint32_t hw = __float_as_uint(rec[3 * j + 2].w);
+            const float4 r0 = rec[3 * j];          // x, y, id, footprint box
+            const uint32_t hw = __float_as_uint(r0.w);
             const float2 h = __half22float2(*reinterpret_cast<const __half2*>(&hw));
             live = !(r0.x < patch.x - h.x) && !(r0.x > patch.z + h.x) && !(r0.y < patch.y - h.y) &&
                    !(r0.y > patch.w + h.y);
@@ -143,22 +145,22 @@ render_forward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ranges
             // survivors of the binning almost always touch some lane, so everything up to the blend is evaluated
             // unconditionally and a single ballot per instance serves both the blend and the n_touched count
             const int j = s_list[warp][k];
-            const float4 r0 = rec[3 * j];          // x, y, conic.x, conic.y
-            const float4 r1 = rec[3 * j + 1];      // conic.z, opacity, depth, id
+            const float4 r0 = rec[3 * j];          // x, y, id, footprint box
+            const float4 r1 = rec[3 * j + 1];      // conic.x, conic.y, conic.z, opacity
             const float dx = fsub(r0.x, pixfx), dy = fsub(r0.y, pixfy);
-            const float power = gauss_power_ref(dx, dy, r0.z, r0.w, r1.x);
+            const float power = gauss_power_ref(dx, dy, r1.x, r1.y, r1.z);
             // alpha = min(0.99, opacity * exp(power)); 1/255 cut; transmittance test (forward.cu:350-363)
-            const float alpha = fminf(0.99f, fmul(r1.y, expf(power)));
+            const float alpha = fminf(0.99f, fmul(r1.w, expf(power)));
             const float test_T = fmul(T, fsub(1.0f, alpha));
             bool act = !done && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
             if (act && test_T < 0.0001f) { done = true; act = false; }
             if (act) {
-                const float4 r2 = rec[3 * j + 2];  // r, g, b
+                const float4 r2 = rec[3 * j + 2];  // r, g, b, depth
                 // C += c * alpha * T as fma(T, alpha*c, C) (reference SASS order)
                 C0 = ffma(T, fmul(alpha, r2.x), C0);
                 C1 = ffma(T, fmul(alpha, r2.y), C1);
                 C2 = ffma(T, fmul(alpha, r2.z), C2);
-                Dp = ffma(T, fmul(alpha, r1.z), Dp);
+                Dp = ffma(T, fmul(alpha, r2.w), Dp);
                 T = test_T;
                 last_contributor = (uint32_t)(b * kBatch + j + 1);
             }
@@ -177,7 +179,7 @@ render_forward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ranges
         if (threadIdx.x < cnt) {
             const int c = s_cnt[stage][threadIdx.x];
             if (c) {
-                atomicAdd(&n_touched[__float_as_int(rec[3 * threadIdx.x + 1].w)], c);
+                atomicAdd(&n_touched[__float_as_int(rec[3 * threadIdx.x].z)], c);
                 s_cnt[stage][threadIdx.x] = 0;
             }
         }
@@ -218,51 +220,124 @@ void launch_render_forward(int W, int H, int grid_x, int grid_y, const uint2* ra
 // =====================================================================================================
 // backward
 // =====================================================================================================
-// Recursive-halving all-lane reduction of 10 values: after the five exchange rounds the lane with
-// bit0 == 0 and index k = 5*bit4 + 3*bit3 + 2*bit2 + bit1 (when valid) holds the warp total of value k.
-__device__ __forceinline__ float warp_reduce10(const float (&v)[10], uint32_t lane) {
-    const bool h16 = lane & 16, h8 = lane & 8, h4 = lane & 4, h2 = lane & 2;
-    float a[5];
-#pragma unroll
-    for (int k = 0; k < 5; ++k) {
-        const float send = h16 ? v[k] : v[k + 5];
-        const float keep = h16 ? v[k + 5] : v[k];
-        a[k] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
-    }
-    float b[3];
-#pragma unroll
-    for (int k = 0; k < 3; ++k) {
-        const float hi = (k + 3 < 5) ? a[k + 3] : 0.0f;
-        const float send = h8 ? a[k] : hi;
-        const float keep = h8 ? hi : a[k];
-        b[k] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
-    }
-    float c[2];
-#pragma unroll
-    for (int k = 0; k < 2; ++k) {
-        const float hi = (k + 2 < 3) ? b[k + 2] : 0.0f;
-        const float send = h4 ? b[k] : hi;
-        const float keep = h4 ? hi : b[k];
-        c[k] = keep + __shfl_xor_sync(0xffffffffu, send, 4);
-    }
-    float d;
-    {
-        const float send = h2 ? c[0] : c[1];
-        const float keep = h2 ? c[1] : c[0];
-        d = keep + __shfl_xor_sync(0xffffffffu, send, 2);
-    }
-    d += __shfl_xor_sync(0xffffffffu, d, 1);
-    return d;
+// Back-to-front over the same records and per-warp lists as the forward. The pixel-major pass replays the blend
+// decisions exactly (same power / expf / alpha sequence) and produces, per (pixel, Gaussian), only the two scalars that
+// all ten per-Gaussian gradient terms are linear in,
+//     u = G * dL/dalpha        (the five geometric moments and dL/dopacity)
+//     w = alpha * T            (colour and depth terms),
+// with dL/dalpha = T q - D / (1 - alpha), q = <colour/depth of this Gaussian, dL/dpixel> and the single running scalar
+// D = <everything blended behind it (absolute weights alpha_j T_j) plus the background share T_final * bg, dL/dpixel>,
+// D += alpha T q (algebraically backward.cu:705-743 without the per-channel "colour behind" recursion).
+// u and w are parked in shared memory, one row of 32 pixels per Gaussian. Once a warp has collected C Gaussians it
+// switches roles: lane = (Gaussian g, 32/C-th part of the patch) walks over its pixels and accumulates the ten sums
+// in registers. The pixel offsets inside an 8 x 4 patch are compile-time constants, so the moments are taken about
+// the patch origin with immediates,
+//     S0 = sum u,  Sx = sum u x,  Sxx = sum u x^2      per patch row (y is constant in a row),
+// and shifted to the Gaussian's centre once per row (dx = gx - x, dy = gy - row). This replaces a cross-lane
+// reduction of ten values per (warp, Gaussian) - 12 SHFL, 22 selects, 12 adds and the ten products feeding them in
+// the round-1 kernel - by ~13 instructions, and the warp's ten totals of a Gaussian leave as three vector REDs
+// (16 + 16 + 8 bytes, SASS REDG.F32x4 / F32x2) from one lane instead of ten scalar lanes.
+// Everything that is constant per Gaussian (opacity, conic, the -0.5 and the NDC scale, backward.cu:745-770) is applied
+// afterwards by the per-Gaussian backward (preprocess_bwd.cu) to the packed sums
+//     {sum u dx, sum u dy, sum u dx^2, sum u dx dy | sum u dy^2, sum u, r, g | b, depth, -, -}.
+template <int C>
+struct BwdLayout {
+    static constexpr int kRowF2 = 33;      // float2 per parked Gaussian: 32 pixels x (u, w) + 1 pad. 66 words = 2 mod 32:
+                                           // the 16 rows a half-warp reads with 64-bit loads in the transposed phase
+                                           // start in 16 different even banks; the pixel-major stores are contiguous
+    static constexpr int kWarps = SPLAT_TILE_PIXELS / 32;
+    static constexpr int kStages = 4;      // record ring: kStages batches of kRecs records in flight per CTA
+    static constexpr int kRecs = 64;
+    static constexpr size_t kRecOff = 0;                                         // float4 [kStages][kRecs * 3]
+    static constexpr size_t kUwOff = kRecOff + kStages * kRecs * 48;             // float2 [kWarps][C][kRowF2]
+    static constexpr size_t kInfoOff = kUwOff + (size_t)kWarps * C * kRowF2 * 8; // float4 [kWarps][C]  x, y, id, -
+    static constexpr size_t kDlpOff = kInfoOff + (size_t)kWarps * C * 16;        // float4 [256] dL/dpixel
+    static constexpr size_t kListOff = kDlpOff + SPLAT_TILE_PIXELS * 16;         // uint8  [kWarps][kRecs]
+    static constexpr size_t kBarOff = kListOff + (size_t)kWarps * kRecs;         // uint64 [kStages] "stage is full"
+    static constexpr size_t kDoneOff = kBarOff + kStages * 8;                    // int    [kStages] warps done with it
+    static constexpr size_t kBytes = kDoneOff + kStages * 4;
+};
+
+__device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
+    asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+__device__ __forceinline__ void red_add_v2(float* addr, float a, float b) {
+    asm volatile("red.global.add.v2.f32 [%0], {%1, %2};" ::"l"(addr), "f"(a), "f"(b) : "memory");
 }
 
-__global__ void __launch_bounds__(SPLAT_TILE_PIXELS)
-render_backward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ranges, const float* __restrict__ records,
-                       const float* __restrict__ bg, const float* __restrict__ final_Ts,
-                       const uint32_t* __restrict__ n_contrib, const float* __restrict__ dL_dpixels,
-                       const float* __restrict__ dL_dpixels_depth, float* __restrict__ grad_accum) {
-    __shared__ __align__(128) float4 s_rec[2][kBatch * 3];
-    __shared__ __align__(8) uint64_t s_bar[2];
-    __shared__ uint8_t s_list[SPLAT_TILE_PIXELS / 32][kBatch];
+// Transposed phase: sums of one chunk of `count` (<= C) parked Gaussians over the warp's 32 pixels.
+template <int C>
+__device__ __forceinline__ void flush_chunk(const float2* __restrict__ uw, const float4* __restrict__ info,
+                                            const float4* __restrict__ dlp, int count, float patch_x0, float patch_y0,
+                                            uint32_t lane, float* __restrict__ grad_accum) {
+    constexpr int kParts = 32 / C, kRows = 4 / kParts;
+    const int g = (int)lane & (C - 1), part = (int)lane / C;
+    const float4 inf = info[g];                                            // x, y, id
+    const float gxr = inf.x - patch_x0, gyr = inf.y - patch_y0;
+    float m0 = 0.f, mx = 0.f, my = 0.f, mxx = 0.f, mxy = 0.f, myy = 0.f, c0 = 0.f, c1 = 0.f, c2 = 0.f, cd = 0.f;
+#pragma unroll
+    for (int rr = 0; rr < kRows; ++rr) {
+        const int row = part * kRows + rr;
+        const float2* urow = uw + g * BwdLayout<C>::kRowF2 + row * 8;
+        const float4* drow = dlp + row * 8;
+        float S0 = 0.f, Sx = 0.f, Sxx = 0.f;
+#pragma unroll
+        for (int x = 0; x < 8; ++x) {
+            const float2 v = urow[x];
+            const float4 d = drow[x];
+            S0 += v.x;
+            Sx = fmaf(v.x, (float)x, Sx);
+            Sxx = fmaf(v.x, (float)(x * x), Sxx);
+            c0 = fmaf(v.y, d.x, c0);
+            c1 = fmaf(v.y, d.y, c1);
+            c2 = fmaf(v.y, d.z, c2);
+            cd = fmaf(v.y, d.w, cd);
+        }
+        // shift the row's moments from the patch origin to the Gaussian's centre: dx = gxr - x, dy = gyr - row
+        const float dy = gyr - (float)row;
+        const float rx = fmaf(gxr, S0, -Sx);                               // sum u dx
+        const float rxx = fmaf(gxr, rx - Sx, Sxx);                         // sum u dx^2
+        m0 += S0;
+        mx += rx;
+        my = fmaf(dy, S0, my);
+        mxx += rxx;
+        mxy = fmaf(dy, rx, mxy);
+        myy = fmaf(dy * dy, S0, myy);
+    }
+#pragma unroll
+    for (int o = 16; o >= C; o >>= 1) {
+        m0 += __shfl_xor_sync(0xffffffffu, m0, o);
+        mx += __shfl_xor_sync(0xffffffffu, mx, o);
+        my += __shfl_xor_sync(0xffffffffu, my, o);
+        mxx += __shfl_xor_sync(0xffffffffu, mxx, o);
+        mxy += __shfl_xor_sync(0xffffffffu, mxy, o);
+        myy += __shfl_xor_sync(0xffffffffu, myy, o);
+        c0 += __shfl_xor_sync(0xffffffffu, c0, o);
+        c1 += __shfl_xor_sync(0xffffffffu, c1, o);
+        c2 += __shfl_xor_sync(0xffffffffu, c2, o);
+        cd += __shfl_xor_sync(0xffffffffu, cd, o);
+    }
+    if (part == 0 && g < count) {
+        float* dst = grad_accum + (size_t)__float_as_uint(inf.z) * SPLAT_GRAD_FLOATS;
+        red_add_v4(dst, mx, my, mxx, mxy);
+        red_add_v4(dst + 4, myy, m0, c0, c1);
+        red_add_v2(dst + 8, c2, cd);
+    }
+}
+
+template <int C>
+__global__ void __launch_bounds__(SPLAT_TILE_PIXELS, C == 8 ? 5 : 4)
+render_backward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ranges,
+                       const float* __restrict__ records, const float* __restrict__ bg,
+                       const float* __restrict__ final_Ts, const uint32_t* __restrict__ n_contrib,
+                       const float* __restrict__ dL_dpixels, const float* __restrict__ dL_dpixels_depth,
+                       float* __restrict__ grad_accum) {
+    using L = BwdLayout<C>;
+    constexpr int kRecs = L::kRecs, kStages = L::kStages;
+    extern __shared__ __align__(128) unsigned char smem[];
+    float4 (*s_rec)[kRecs * 3] = reinterpret_cast<float4 (*)[kRecs * 3]>(smem + L::kRecOff);
+    uint64_t* s_full = reinterpret_cast<uint64_t*>(smem + L::kBarOff);
+    int* s_done = reinterpret_cast<int*>(smem + L::kDoneOff);
 
     const int tile = blockIdx.x;
     const int tile_x = tile % grid_x, tile_y = tile / grid_x;
@@ -273,31 +348,35 @@ render_backward_kernel(int W, int H, int grid_x, const uint2* __restrict__ range
     const float pixfx = (float)px, pixfy = (float)py;
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const float4 patch = patch_of_warp(tile_x, tile_y);
+    uint8_t* s_list = smem + L::kListOff + warp * kRecs;
+    const float2* s_uw = reinterpret_cast<const float2*>(smem + L::kUwOff) + (size_t)warp * C * L::kRowF2;
+    const float4* s_info = reinterpret_cast<const float4*>(smem + L::kInfoOff) + warp * C;
+    float4* s_dlp = reinterpret_cast<float4*>(smem + L::kDlpOff) + warp * 32;
+    // 32-bit shared addresses for the stores of the hot loop: this lane's column of the next free row, and its info slot
+    const uint32_t uw_first = smem_u32(s_uw) + lane * 8u;
+    const uint32_t info_first = smem_u32(s_info), info_end = info_first + C * 16u;
+    uint32_t uw_a = uw_first, info_a = info_first;
 
     const uint2 range = ranges[tile];
     const int n = (int)(range.y - range.x);
-    const int nb = (n + kBatch - 1) / kBatch;
+    const int nb = (n + kRecs - 1) / kRecs;
     const float4* src = reinterpret_cast<const float4*>(records) + 3 * (size_t)range.x;
 
     // batch b (counted from the BACK of the list) covers list indices [lo_b, hi_b)
-    auto batch_lo = [&](int b) { return max(0, n - (b + 1) * kBatch); };
-    auto batch_hi = [&](int b) { return n - b * kBatch; };
+    auto batch_lo = [&](int b) { return max(0, n - (b + 1) * kRecs); };
+    auto batch_hi = [&](int b) { return n - b * kRecs; };
+    auto fill = [&](int b) {   // one thread: bulk copy of batch b into its ring stage
+        const int lo = batch_lo(b), cnt = batch_hi(b) - lo;
+        bulk_load(&s_rec[b % kStages][0], src + 3 * (size_t)lo, (uint32_t)cnt * 48u, &s_full[b % kStages]);
+    };
 
-    if (threadIdx.x == 0) { mbar_init(&s_bar[0], 1); mbar_init(&s_bar[1], 1); fence_mbar_init(); }
-    __syncthreads();
     if (threadIdx.x == 0) {
-        for (int b = 0; b < 2 && b < nb; ++b) {
-            const int lo = batch_lo(b), cnt = batch_hi(b) - lo;
-            bulk_load(&s_rec[b][0], src + 3 * (size_t)lo, (uint32_t)cnt * 48u, &s_bar[b]);
-        }
+        for (int st = 0; st < kStages; ++st) { mbar_init(&s_full[st], 1); s_done[st] = 0; }
+        fence_mbar_init();
     }
-
-    // which of the 10 reduced terms this lane ends up holding (see warp_reduce10), and where it goes in the
-    // packed accumulator {sum u dx, sum u dy, sum u dx^2, sum u dx dy, sum u dy^2, sum u, r, g, b, depth, -, -}
-    const int inner3 = ((lane >> 2) & 1) * 2 + ((lane >> 1) & 1);
-    const int inner5 = ((lane >> 3) & 1) * 3 + inner3;
-    const int my_k = ((lane >> 4) & 1) * 5 + inner5;
-    const bool holder = ((lane & 1) == 0) && inner3 < 3 && inner5 < 5;
+    __syncthreads();
+    if (threadIdx.x == 0)
+        for (int b = 0; b < kStages && b < nb; ++b) fill(b);
 
     const float T_final = inside ? final_Ts[pix_id] : 0.0f;
     float T = T_final;
@@ -308,90 +387,123 @@ render_backward_kernel(int W, int H, int grid_x, const uint2* __restrict__ range
         dLp0 = dL_dpixels[pix_id]; dLp1 = dL_dpixels[HW + pix_id]; dLp2 = dL_dpixels[2 * HW + pix_id];
         dLpd = dL_dpixels_depth[pix_id];
     }
-    // D = <what lies behind the Gaussian being processed, dL/dpixel>; behind the last one there is only the background
+    s_dlp[lane] = make_float4(dLp0, dLp1, dLp2, dLpd);     // read back by the other lanes of this warp only
+    // behind the last Gaussian there is only the background
     float D = T_final * (bg[0] * dLp0 + bg[1] * dLp1 + bg[2] * dLp2);
-
-    // nothing in this warp ever blended anything -> the warp only helps with barriers
+    // nothing in this warp ever blended anything -> the warp only keeps the ring going
     const int warp_last = __reduce_max_sync(0xffffffffu, last_contributor);
 
+    // The warps of a tile see very different numbers of Gaussians (per-warp binning), so they do not meet at a block
+    // barrier per batch: every warp walks the ring at its own pace, waiting only for "stage full" (mbarrier completed
+    // by the bulk copy). When a warp is done with a stage its lane 0 counts itself off; the LAST warp to do so
+    // re-arms the stage with the batch kStages further on. A fast warp can thus run up to kStages - 1 batches ahead.
     for (int b = 0; b < nb; ++b) {
-        const int stage = b & 1;
+        const int stage = b % kStages;
         const int lo = batch_lo(b), cnt = batch_hi(b) - lo;
-        mbar_wait(&s_bar[stage], (uint32_t)((b >> 1) & 1));
+        mbar_wait(&s_full[stage], (uint32_t)((b / kStages) & 1));
         const float4* rec = &s_rec[stage][0];
         if (lo < warp_last) {
             // only list positions below the warp's deepest contributor matter; bin them against the warp's patch
-            const int n_live = bin_batch_for_warp(rec, min(cnt, warp_last - lo), patch, s_list[warp], lane);
+            const int n_live = bin_batch_for_warp<kRecs>(rec, min(cnt, warp_last - lo), patch, s_list, lane);
+            const int lc_rel = last_contributor - lo;      // the pixel's last contributor, relative to this batch
             for (int k = n_live - 1; k >= 0; --k) {
-                const int j = s_list[warp][k];
-                const int idx = lo + j;                        // position in the tile's list
-                const float4 r0 = rec[3 * j];
-                const float4 r1 = rec[3 * j + 1];
+                const int j = s_list[k];
+                const float4 r0 = rec[3 * j];              // x, y, id, footprint box
+                const float4 r1 = rec[3 * j + 1];          // conic.x, conic.y, conic.z, opacity
                 const float dx = fsub(r0.x, pixfx), dy = fsub(r0.y, pixfy);
-                const float power = gauss_power_ref(dx, dy, r0.z, r0.w, r1.x);
+                const float power = gauss_power_ref(dx, dy, r1.x, r1.y, r1.z);
                 // same expf / alpha as the forward so that the blend decisions replay exactly
                 const float G0 = expf(power);
-                const float alpha0 = fminf(0.99f, fmul(r1.y, G0));
-                const bool skip = (idx >= last_contributor) || (power > 0.0f) || (alpha0 < 1.0f / 255.0f);
+                const float alpha0 = fminf(0.99f, fmul(r1.w, G0));
+                const bool skip = (j >= lc_rel) || (power > 0.0f) || (alpha0 < 1.0f / 255.0f);
                 if (__all_sync(0xffffffffu, skip)) continue;
-                const float4 r2 = rec[3 * j + 2];
-                // lanes that skip contribute through G = 0 and alpha = 0 (two selects instead of ten)
+                const float4 r2 = rec[3 * j + 2];          // r, g, b, depth
+                // lanes that skip contribute through G = 0 and alpha = 0
                 const float G = skip ? 0.0f : G0;
                 const float alpha = skip ? 0.0f : alpha0;
                 float inv;
                 asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(inv) : "f"(1.0f - alpha));
-                // transmittance in front of this Gaussian (backward.cu:700)
-                T = skip ? T : T * inv;
-                // dL/dalpha (backward.cu:705-743) without the per-channel "colour behind" recursion: with
-                // q = <colour/depth of this Gaussian, dL/dpixel> and D = <everything blended behind it (in absolute
-                // weights alpha_j T_j) plus the background share T_final * bg, dL/dpixel>,
-                //   sum_c (c - accum_rec_c) dL_c * T - T_final/(1-alpha) * <bg, dL>  =  T q - D / (1 - alpha),
-                // and D grows by alpha T q. One scalar of state instead of nine, 7 operations instead of ~20.
-                const float w = alpha * T;                                   // dchannel_dcolor
-                const float q = r2.x * dLp0 + r2.y * dLp1 + r2.z * dLp2 + r1.z * dLpd;
+                T = skip ? T : T * inv;                    // transmittance in front of this Gaussian (backward.cu:700)
+                const float w = alpha * T;
+                const float q = r2.x * dLp0 + r2.y * dLp1 + r2.z * dLp2 + r2.w * dLpd;
                 const float dL_dalpha = T * q - inv * D;
                 D = w * q + D;
-                const float dchannel_dcolor = w;
-
-                // Everything that is constant per Gaussian (opacity, conic, the -0.5 and the NDC scale) is factored out
-                // of the pixel sum: the warp reduces the moments of u = G * dL/dalpha over its pixels,
-                //   sum u dx, sum u dy, sum u dx^2, sum u dx dy, sum u dy^2, sum u,
-                // and the per-Gaussian backward turns them into dL/dmean2D, dL/dconic, dL/dopacity
-                // (backward.cu:745-770; preprocess_bwd.cu: moments_to_gradients).
-                const float u = G * dL_dalpha;
-                const float ux = u * dx, uy = u * dy;
-                float v[10];
-                v[0] = ux;
-                v[1] = uy;
-                v[2] = ux * dx;
-                v[3] = ux * dy;
-                v[4] = uy * dy;
-                v[5] = u;
-                v[6] = dchannel_dcolor * dLp0;
-                v[7] = dchannel_dcolor * dLp1;
-                v[8] = dchannel_dcolor * dLp2;
-                v[9] = dchannel_dcolor * dLpd;
-                const float total = warp_reduce10(v, lane);
-                if (holder && total != 0.0f) {
-                    const uint32_t id = __float_as_uint(r1.w);
-                    atomicAdd(&grad_accum[(size_t)id * SPLAT_GRAD_FLOATS + my_k], total);
+                // park (u, w) of this pixel in the Gaussian's row; lane 0 adds the Gaussian's x, y, id
+                asm volatile(
+                    "{\n\t.reg .pred p;\n\t"
+                    "st.shared.v2.f32 [%0], {%1, %2};\n\t"
+                    "setp.eq.u32 p, %3, 0;\n\t"
+                    "@p st.shared.v4.f32 [%4], {%5, %6, %7, %8};\n\t}"
+                    ::"r"(uw_a), "f"(G * dL_dalpha), "f"(w), "r"(lane), "r"(info_a), "f"(r0.x), "f"(r0.y), "f"(r0.z),
+                      "f"(r0.w)
+                    : "memory");
+                uw_a += L::kRowF2 * 8u;
+                info_a += 16u;
+                if (info_a == info_end) {
+                    __syncwarp();
+                    flush_chunk<C>(s_uw, s_info, s_dlp, C, patch.x, patch.y, lane, grad_accum);
+                    __syncwarp();
+                    uw_a = uw_first;
+                    info_a = info_first;
                 }
             }
         }
-        __syncthreads();
-        if (threadIdx.x == 0 && b + 2 < nb) {
-            const int lo2 = batch_lo(b + 2), cnt2 = batch_hi(b + 2) - lo2;
-            fence_proxy_async();
-            bulk_load(&s_rec[stage][0], src + 3 * (size_t)lo2, (uint32_t)cnt2 * 48u, &s_bar[stage]);
+        __syncwarp();                                      // every lane has read what it needs from this stage
+        if (lane == 0) {
+            __threadfence_block();
+            if (atomicAdd(&s_done[stage], 1) == L::kWarps - 1) {
+                s_done[stage] = 0;                         // published to the other warps by the refill's mbarrier
+                if (b + kStages < nb) {
+                    __threadfence_block();
+                    fence_proxy_async();
+                    fill(b + kStages);
+                }
+            }
         }
     }
+    if (info_a != info_first) {
+        __syncwarp();
+        flush_chunk<C>(s_uw, s_info, s_dlp, (int)((info_a - info_first) >> 4), patch.x, patch.y, lane, grad_accum);
+    }
+}
+
+template <int C>
+static void launch_bwd_chunked(int W, int H, int grid_x, int grid_y, const uint2* ranges, const float* records,
+                               const float* bg, const float* final_T, const uint32_t* n_contrib, const float* dL_dpix,
+                               const float* dL_dpix_depth, float* grad_accum, cudaStream_t s) {
+    // opt in to more than 48 KB of shared memory once per device
+    static bool configured[64];
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev >= 0 && dev < 64 && !configured[dev]) {
+        cudaFuncSetAttribute(render_backward_kernel<C>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             (int)BwdLayout<C>::kBytes);
+        configured[dev] = true;
+    }
+    render_backward_kernel<C><<<grid_x * grid_y, SPLAT_TILE_PIXELS, BwdLayout<C>::kBytes, s>>>(
+        W, H, grid_x, ranges, records, bg, final_T, n_contrib, dL_dpix, dL_dpix_depth, grad_accum);
+}
+
+// Chunk size of the transposed phase: 8 (default) or 16 Gaussians per warp. Measured on the bench scene (B200):
+// 16 is the faster kernel when it runs alone (0.441 vs 0.457 ms: fewer shuffles per Gaussian), 8 needs 35 KB of shared
+// memory and 48 registers instead of 53 KB and 64, leaves room for the other views' kernels and wins when several
+// views are in flight (906 vs 878 it/s with five view streams). SPLAT_BWD_CHUNK=16 selects the other one.
+static int bwd_variant() {
+    static int v = -1;
+    if (v < 0) {
+        const char* e = getenv("SPLAT_BWD_CHUNK");
+        v = (e && atoi(e) == 16) ? 16 : 8;
+    }
+    return v;
 }
 
 void launch_render_backward(int W, int H, int grid_x, int grid_y, const uint2* ranges, const float* records,
                             const float* bg, const float* final_T, const uint32_t* n_contrib, const float* dL_dpix,
                             const float* dL_dpix_depth, float* grad_accum, cudaStream_t s) {
-    render_backward_kernel<<<grid_x * grid_y, SPLAT_TILE_PIXELS, 0, s>>>(W, H, grid_x, ranges, records, bg, final_T,
-                                                                         n_contrib, dL_dpix, dL_dpix_depth, grad_accum);
+    if (bwd_variant() == 8)
+        launch_bwd_chunked<8>(W, H, grid_x, grid_y, ranges, records, bg, final_T, n_contrib, dL_dpix, dL_dpix_depth, grad_accum, s);
+    else
+        launch_bwd_chunked<16>(W, H, grid_x, grid_y, ranges, records, bg, final_T, n_contrib, dL_dpix, dL_dpix_depth, grad_accum, s);
 }
 
 }  // namespace splat
