@@ -2,22 +2,34 @@
 """bench.py — fwd+bwd rasterization throughput of the B200-native Gaussian rasterizer (BASELINE.json metric).
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--scaling weak|strong]
+                    [--workload replica|scannet] [--verify]
     python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P \
            bench.py --gpus N --steps K --warmup W
 
-Workload (config.workload): Replica-shape 1200x680 camera, 1M synthetic Gaussians, SH degree 0, a mapping window
-of 10 keyframe views per GPU; one "step" = every view of the rank's window forward + backward with pose
-gradients through the public API (`GaussianRasterizer(...)` + autograd), the Gaussian gradients accumulating in
-one flat buffer, then (N > 1) ONE NCCL all-reduce of that buffer.  One "it" of the metric = one view fwd+bwd.
+Workload (config.workload), default `replica` = BASELINE config 4's shape: Replica 1200x680 camera, 1M synthetic
+Gaussians, SH degree 0, a mapping window of 10 keyframe views per GPU; one "step" = every view of the rank's window
+forward + backward with pose gradients through the public API (`GaussianRasterizer(...)` + autograd), the Gaussian
+gradients accumulating in one flat buffer, then (N > 1) ONE exchange of that buffer.  One "it" of the metric = one
+view fwd+bwd.  `--workload scannet` = BASELINE config 5: 1296x968, 3M Gaussians, SH degree 3, ONE view per rank and
+step (final refinement renders one keyframe per iteration, reference src/mapper.py:664-699), 708 MB exchanged.
 
   value : views/s over all ranks, inputs resident in HBM, CUDA-event timed, max over ranks.
   e2e   : the same step with each view's camera matrices and upstream-gradient images copied host->device
           from pinned memory inside the timed region and the step's scalar result read back.
-  roofline : dominant kernel (render_backward), algorithmic bytes (84*R + 24*N) / its live
-          CUDA-event duration, against MEASURED_PEAKS.json hbm_gbs.
+  value_single_stream / e2e_single_stream : the same two legs with every view on the caller's stream and no priority
+          lanes, i.e. what an UNMODIFIED src/mapper.py gets; `value`/`e2e` need the caller to issue its views through
+          `window.ViewStreams`.
+  strong (N > 1, replica): the FIXED 10-view window of BASELINE config 4 sharded over the N ranks (ceiling
+          views / max views per rank), measured in the same run.
+  configs (N = 1): ms per iteration of BASELINE configs 2, 3 and 5 through the same API, one stream; the reference arm
+          prints the same list for the reference extension.
+  roofline : dominant kernel, algorithmic bytes / its live CUDA-event duration, against
+          MEASURED_PEAKS.json hbm_gbs.
   cpu_baseline : the CPU oracle (pure PyTorch port) on BASELINE config 1 (100k Gaussians, 640x480, 1 view).
   --impl reference : the UNMODIFIED reference CUDA extension (oracle/_ref/ref_dgr, sm_100 build) on the same
           workload through its own public API; falls back to the CPU oracle if that build is absent.
+  --verify : after the timed legs, one more step whose exchanged gradient buffer is checksummed on every rank (the
+          sums must be identical on all ranks) and, at N > 1, compared with the same views rendered by rank 0 alone.
 """
 from __future__ import annotations
 
@@ -38,10 +50,16 @@ for p in (ROOT, os.path.join(ROOT, "splat-slam_b200"), os.path.join(ROOT, "oracl
 import torch  # noqa: E402
 import torch.distributed as dist  # noqa: E402
 
-CAMERA = "replica"
-P_GAUSS = 1_000_000
-VIEWS_PER_RANK = 10
-METRIC = "fwd+bwd rasterize it/s @1200x680, 1M Gaussians"
+WORKLOADS = {
+    "replica": dict(camera="replica", gaussians=1_000_000, sh_coeffs=1, sh_degree=0, views=10,
+                    metric="fwd+bwd rasterize it/s @1200x680, 1M Gaussians"),
+    "scannet": dict(camera="scannet", gaussians=3_000_000, sh_coeffs=16, sh_degree=3, views=1,
+                    metric="fwd+bwd rasterize it/s @1296x968, 3M Gaussians, SH degree 3 (BASELINE config 5)"),
+}
+# dram__bytes_read.sum + dram__bytes_write.sum per launch of the render kernels on the default scene, from the
+# ncu --set full capture of this round (the file named here); not re-measured by this run
+TRAFFIC = {"source": "profiles/r02_render_ncu_summary.md (ncu --set full, bench scene, one launch)",
+           "render_backward": 249.2e6, "render_forward": 174.6e6}
 
 
 def parse():
@@ -51,15 +69,28 @@ def parse():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"])
-    ap.add_argument("--gaussians", type=int, default=P_GAUSS)
-    ap.add_argument("--views", type=int, default=VIEWS_PER_RANK)
-    ap.add_argument("--camera", default=CAMERA)
+    ap.add_argument("--workload", default="replica", choices=sorted(WORKLOADS))
+    ap.add_argument("--gaussians", type=int, default=None)
+    ap.add_argument("--views", type=int, default=None)
+    ap.add_argument("--camera", default=None)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extras", action="store_true", help="skip the single-stream legs, the strong sub-record and "
+                    "the other BASELINE configs (only the main value / e2e legs and the stage profile)")
+    ap.add_argument("--verify", action="store_true")
+    ap.add_argument("--exchange", default="auto", choices=["auto", "nccl", "peer"],
+                    help="gradient exchange at N > 1: this library's peer-memory all-reduce kernel or NCCL")
     ap.add_argument("--priority-lanes", type=int, default=1, help="1: short kernels on a high-priority side stream")
     ap.add_argument("--streams", type=int, default=5,
                     help="views of a step are issued round-robin on this many CUDA streams (ours only; the reference "
                          "extension launches on the legacy default stream and always runs with 1)")
-    return ap.parse_args()
+    a = ap.parse_args()
+    w = WORKLOADS[a.workload]
+    a.camera = a.camera or w["camera"]
+    a.gaussians = a.gaussians or w["gaussians"]
+    a.views = a.views or w["views"]
+    a.sh_coeffs, a.sh_degree, a.metric = w["sh_coeffs"], w["sh_degree"], w["metric"]
+    a.default_scene = (a.workload == "replica" and a.camera == w["camera"] and a.gaussians == w["gaussians"])
+    return a
 
 
 # ---------------------------------------------------------------------------------------------------------
@@ -125,19 +156,25 @@ class ClockSampler:
 class Workload:
     """Gaussians (resident on the device, like model weights), the rank's views and upstream gradients."""
 
-    def __init__(self, mod, args, device, rank, world):
+    def __init__(self, mod, args, device, rank, world, scaling, shared=None, streams=None, exchange="nccl"):
         from diff_gaussian_rasterization import synthetic as syn
         from diff_gaussian_rasterization.window import FlatGrads, ViewStreams, partition_views
-        self.mod, self.device, self.syn = mod, device, syn
-        g = syn.make_gaussians(args.camera, args.gaussians, seed=0, sh_coeffs=1)
-        self.params = {k: g[k].to(device).requires_grad_(True) for k in ("means3D", "shs", "opacities", "scales", "rotations")}
-        self.flat = FlatGrads(self.params)
-        if args.scaling == "weak":
+        self.mod, self.device, self.syn, self.args = mod, device, syn, args
+        self.ours = mod.__name__ == "diff_gaussian_rasterization"
+        if shared is None:
+            g = syn.make_gaussians(args.camera, args.gaussians, seed=0, sh_coeffs=args.sh_coeffs)
+            self.params = {k: g[k].to(device).requires_grad_(True)
+                           for k in ("means3D", "shs", "opacities", "scales", "rotations")}
+            self.flat = FlatGrads(self.params, exchange=exchange if world > 1 else "nccl")
+        else:
+            self.params, self.flat = shared.params, shared.flat
+        if scaling == "weak":
             self.view_ids = [rank * args.views + i for i in range(args.views)]
             self.global_views = args.views * world
         else:
             self.view_ids = partition_views(args.views, world, rank)
             self.global_views = args.views
+        self.scaling, self.world = scaling, world
         W, H = syn.CAMERAS[args.camera][:2]
         self.W, self.H = W, H
         self.host_views = [syn.make_view(args.camera, syn.window_pose(v)) for v in self.view_ids]
@@ -147,29 +184,40 @@ class Workload:
                                     torch.cat([v.campos, torch.zeros(13)])]).pin_memory() for v in self.host_views]
         self.h_up = torch.cat([Wc, Wd]).contiguous().pin_memory()           # (4,H,W)
         self.d_mats = [m.to(device) for m in self.h_mats]
-        self.d_up = self.h_up.to(device)
+        self.d_up = self.h_up.to(device) if shared is None else shared.d_up
         self.bg = torch.zeros(3, device=device)
         self.theta = [torch.zeros(3, device=device, requires_grad=True) for _ in self.view_ids]
         self.rho = [torch.zeros(3, device=device, requires_grad=True) for _ in self.view_ids]
         self.means2D = torch.zeros_like(self.params["means3D"], requires_grad=True)
-        # e2e leg: double-buffered device staging filled by a copy stream, so the next view's H2D overlaps compute
-        self.streams = ViewStreams(device, args.streams if mod.__name__ == "diff_gaussian_rasterization" else 1,
-                                   priority_lanes=bool(args.priority_lanes))
-        self.nbuf = max(2, len(self.streams) + 1)      # one staging buffer per view in flight, plus the one being filled
+        self.set_streams(args.streams if streams is None else streams, bool(args.priority_lanes))
+        self.copy_stream = torch.cuda.Stream(device=device)
+        self.last = {}
+
+    def set_streams(self, n, lanes):
+        """(Re)build the view streams and the e2e staging ring: one buffer per view in flight plus the one being
+        filled by the copy stream, so the next view's H2D overlaps compute."""
+        from diff_gaussian_rasterization.window import ViewStreams
+        old = getattr(self, "streams", None)
+        if old is not None:
+            old.close()
+        self.streams = ViewStreams(self.device, n if self.ours else 1, priority_lanes=lanes)
+        if self.ours:
+            from diff_gaussian_rasterization import _cabi
+            _cabi.priority_lanes(lanes and len(self.streams) > 1)
+        self.nbuf = max(2, len(self.streams) + 1)
         self.stage_mats = [torch.empty_like(self.d_mats[0]) for _ in range(self.nbuf)] if self.d_mats else None
         self.stage_up = [torch.empty_like(self.d_up) for _ in range(self.nbuf)]
-        self.copy_stream = torch.cuda.Stream(device=device)
         self.ev_ready = [torch.cuda.Event() for _ in range(self.nbuf)]
         self.ev_mats = [torch.cuda.Event() for _ in range(self.nbuf)]
         self.ev_free = [torch.cuda.Event() for _ in range(self.nbuf)]
-        self.last = {}
 
     def settings(self, i, mats):
         v = self.host_views[i]
         return self.mod.GaussianRasterizationSettings(
             image_height=v.image_height, image_width=v.image_width, tanfovx=v.tanfovx, tanfovy=v.tanfovy, bg=self.bg,
             scale_modifier=1.0, viewmatrix=mats[0].view(4, 4), projmatrix=mats[1].view(4, 4),
-            projmatrix_raw=mats[2].view(4, 4), sh_degree=0, campos=mats[3][:3], prefiltered=False, debug=False)
+            projmatrix_raw=mats[2].view(4, 4), sh_degree=self.args.sh_degree, campos=mats[3][:3], prefiltered=False,
+            debug=False)
 
     def render_backward(self, i, mats, up, up_ready=None):
         p = self.params
@@ -259,8 +307,17 @@ def timed(fn, steps, warmup, device, world):
     return float(ms.item())
 
 
+def legs(wl, args, device, world):
+    """(value it/s, ms per step, e2e it/s, ms per step) of one workload with its current stream setting."""
+    ms_v = timed(wl.step_resident, args.steps, args.warmup, device, world)
+    ms_e = timed(wl.step_e2e, args.steps, max(1, args.warmup // 2), device, world)
+    g = wl.global_views * args.steps
+    return g / (ms_v * 1e-3), ms_v / args.steps, g / (ms_e * 1e-3), ms_e / args.steps
+
+
 def cpu_baseline_port(threads=None):
-    """CPU oracle (pure-PyTorch port) on BASELINE.json config 1: 100k Gaussians, 640x480, one pose, fwd+bwd."""
+    """CPU oracle (pure-PyTorch port) on BASELINE.json config 1: 100k Gaussians, 640x480, one pose, fwd+bwd.
+    One untimed run to warm the allocator / thread pool, then the timed one."""
     from diff_gaussian_rasterization import synthetic as syn
     from oracle import torch_rasterizer as orc
     cores = threads or os.cpu_count() or 1
@@ -271,13 +328,105 @@ def cpu_baseline_port(threads=None):
     Wc, Wd = syn.upstream_grads(cam)
     S = orc.Settings(v.image_height, v.image_width, v.tanfovx, v.tanfovy, torch.zeros(3), 1.0, v.viewmatrix,
                      v.projmatrix, v.projmatrix_raw, 0, v.campos)
-    t0 = time.perf_counter()
-    orc.rasterize(g["means3D"], g["opacities"], S, shs=g["shs"], scales=g["scales"], rotations=g["rotations"],
-                  dL_dcolor=Wc, dL_ddepth=Wd)
-    dt = time.perf_counter() - t0
+    dts = []
+    for _ in range(2):
+        t0 = time.perf_counter()
+        orc.rasterize(g["means3D"], g["opacities"], S, shs=g["shs"], scales=g["scales"], rotations=g["rotations"],
+                      dL_dcolor=Wc, dL_ddepth=Wd)
+        dts.append(time.perf_counter() - t0)
+    dt = dts[-1]
     return {"value": 1.0 / dt, "unit": "it/s", "cores": cores, "kind": "port",
             "sample": "BASELINE config 1: 1 view fwd+bwd, 100k Gaussians, 640x480 (TUM intrinsics), CPU oracle "
-                      f"oracle/torch_rasterizer.py, {dt:.1f} s"}
+                      f"oracle/torch_rasterizer.py; warm-up run {dts[0]:.1f} s, timed run {dt:.1f} s"}
+
+
+def other_configs(mod, device):
+    """BASELINE configs 2, 3 and 5 through the module's public API, one view per iteration on one stream: CUDA-event
+    ms per iteration (median-free mean over the timed iterations after 3 warm-up iterations)."""
+    from diff_gaussian_rasterization import synthetic as syn
+    out = []
+    specs = (("config 2: Replica 1200x680, 500k Gaussians, SH0, fwd+bwd with pose grads", "replica", 500_000, 1, 0, 30, True),
+             ("config 3: TUM 640x480 tracking, pose-only gradients, 200k Gaussians, 100 iterations", "tum", 200_000, 1, 0, 100, False),
+             ("config 5: ScanNet 1296x968, 3M Gaussians, SH3, one view per iteration (1 GPU)", "scannet", 3_000_000, 16, 3, 10, True))
+    for label, cam, P, M, D, iters, gauss_grads in specs:
+        g = syn.make_gaussians(cam, P, seed=0, sh_coeffs=M)
+        leaves = {k: g[k].to(device).requires_grad_(gauss_grads) for k in ("means3D", "shs", "opacities", "scales", "rotations")}
+        views = [syn.make_view(cam, syn.window_pose(v)) for v in range(1, 5)]
+        mats = [[m.to(device) for m in (v.viewmatrix, v.projmatrix, v.projmatrix_raw, v.campos)] for v in views]
+        Wc, Wd = (t.to(device) for t in syn.upstream_grads(cam))
+        bg = torch.zeros(3, device=device)
+        m2d = torch.zeros_like(leaves["means3D"], requires_grad=gauss_grads)
+        theta = torch.zeros(3, device=device, requires_grad=True)
+        rho = torch.zeros(3, device=device, requires_grad=True)
+
+        def step(i):
+            v, m = views[i % 4], mats[i % 4]
+            S = mod.GaussianRasterizationSettings(
+                image_height=v.image_height, image_width=v.image_width, tanfovx=v.tanfovx, tanfovy=v.tanfovy, bg=bg,
+                scale_modifier=1.0, viewmatrix=m[0], projmatrix=m[1], projmatrix_raw=m[2], sh_degree=D, campos=m[3],
+                prefiltered=False, debug=False)
+            color, radii, depth, opacity, n_touched = mod.GaussianRasterizer(S)(
+                means3D=leaves["means3D"], means2D=m2d, opacities=leaves["opacities"], shs=leaves["shs"],
+                scales=leaves["scales"], rotations=leaves["rotations"], theta=theta, rho=rho)
+            torch.autograd.backward([color, depth], [Wc, Wd])
+            for t in leaves.values():
+                t.grad = None
+
+        for i in range(3):
+            step(i)
+        torch.cuda.synchronize(device)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for i in range(iters):
+            step(i)
+        e1.record()
+        torch.cuda.synchronize(device)
+        ms = e0.elapsed_time(e1) / iters
+        out.append({"config": label, "ms_per_it": ms, "it_per_s": 1e3 / ms, "iterations": iters, "streams": 1})
+        del g, leaves, m2d
+        torch.cuda.empty_cache()
+    return out
+
+
+def verify_exchange(wl, args, device, rank, world):
+    """One more step; every rank checksums the exchanged flat gradient buffer (double-precision sum and sum of
+    squares). At N > 1 rank 0 also renders ALL views of the step alone and the relative difference is reported."""
+    wl.step_resident()
+    torch.cuda.synchronize(device)
+    flat = wl.flat.flat.double()
+    mine = torch.stack([flat.sum(), (flat * flat).sum()])
+    sums = [torch.zeros_like(mine) for _ in range(world)]
+    if world > 1:
+        dist.all_gather(sums, mine)
+    else:
+        sums = [mine]
+    rows = [[float(x) for x in s.tolist()] for s in sums]
+    out = {"checksums_sum_sumsq_per_rank": rows, "identical_on_all_ranks": all(r == rows[0] for r in rows)}
+    if world > 1:
+        from diff_gaussian_rasterization import synthetic as syn
+        exchanged = wl.flat.flat.clone()
+        all_ids = []
+        for r in range(world):
+            all_ids += ([r * args.views + i for i in range(args.views)] if wl.scaling == "weak"
+                        else [v for v in range(args.views) if v % world == r])
+        rel = torch.zeros(1, device=device)
+        if rank == 0:
+            wl.flat.flat.zero_()
+            wl.flat.zero_()
+            for v in all_ids:
+                view = syn.make_view(args.camera, syn.window_pose(v))
+                mats = torch.stack([view.viewmatrix.reshape(-1), view.projmatrix.reshape(-1),
+                                    view.projmatrix_raw.reshape(-1), torch.cat([view.campos, torch.zeros(13)])]).to(device)
+                wl.host_views.append(view)
+                wl.theta.append(torch.zeros(3, device=device, requires_grad=True))
+                wl.rho.append(torch.zeros(3, device=device, requires_grad=True))
+                wl.render_backward(len(wl.host_views) - 1, mats, wl.d_up)
+            torch.cuda.synchronize(device)
+            alone = wl.flat.flat
+            rel[0] = (exchanged - alone).abs().max() / alone.abs().max().clamp_min(1e-30)
+        dist.broadcast(rel, 0)
+        out["max_rel_diff_vs_rank0_rendering_all_views"] = float(rel.item())
+    return out
 
 
 def main():
@@ -294,7 +443,7 @@ def main():
     if not torch.cuda.is_available():
         if args.impl == "reference":
             cb = cpu_baseline_port()
-            print(json.dumps({"impl": "reference", "metric": METRIC, "value": cb["value"], "unit": "it/s",
+            print(json.dumps({"impl": "reference", "metric": args.metric, "value": cb["value"], "unit": "it/s",
                               "n_gpus": args.gpus, "steps": 1, "warmup": 0, "higher_is_better": True,
                               "cpu_baseline": cb, "e2e": {"value": cb["value"], "unit": "it/s",
                                                           "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
@@ -303,6 +452,10 @@ def main():
 
     device = torch.device("cuda", local_rank)
     torch.cuda.set_device(device)
+    # the legs switch between one and several view streams; gradient accumulation into the shared leaves crosses streams
+    # on purpose (autograd orders it), so the advisory warning about it is noise here
+    if hasattr(torch.autograd.graph, "set_warn_on_accumulate_grad_stream_mismatch"):
+        torch.autograd.graph.set_warn_on_accumulate_grad_stream_mismatch(False)
     if ref_world > 1:
         dist.init_process_group("nccl", device_id=device)
 
@@ -313,7 +466,7 @@ def main():
             kind = "reference-cuda"
         except Exception as ex:  # reference build absent: time the CPU port instead (tier framing, item 4)
             cb = cpu_baseline_port()
-            print(json.dumps({"impl": "reference", "metric": METRIC, "value": cb["value"], "unit": "it/s",
+            print(json.dumps({"impl": "reference", "metric": args.metric, "value": cb["value"], "unit": "it/s",
                               "n_gpus": n_gpus, "steps": 1, "warmup": 0, "ms_per_step": 1e3 / cb["value"],
                               "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None, "dtype": "f32",
                               "data": "synthetic", "config": {"workload": "BASELINE config 1 (CPU port)"},
@@ -324,7 +477,8 @@ def main():
     else:
         import diff_gaussian_rasterization as mod
 
-    wl = Workload(mod, args, device, rank if ref_world > 1 else 0, ref_world)
+    wrank = rank if ref_world > 1 else 0
+    wl = Workload(mod, args, device, wrank, ref_world, args.scaling, exchange=args.exchange)
     views_per_step_global = wl.global_views
 
     sampler = ClockSampler(local_rank) if rank == 0 else None
@@ -333,18 +487,44 @@ def main():
     launches0 = 0
     if kind == "ours":
         from diff_gaussian_rasterization import _cabi
-        _cabi.priority_lanes(bool(args.priority_lanes) and args.streams > 1)
-    ms_value = timed(wl.step_resident, args.steps, args.warmup, device, ref_world)
+    value, ms_step, e2e, ms_step_e2e = legs(wl, args, device, ref_world)
     if kind == "ours":      # kernels of this library per step, counted by the library itself, x timed steps
         _cabi.launch_count(reset=True)
         wl.step_resident()
         launches0 = _cabi.launch_count(reset=True) * args.steps
-    ms_e2e = timed(wl.step_e2e, args.steps, max(1, args.warmup // 2), device, ref_world)
     clocks = sampler.stop() if sampler else None
-
     n_streams = max(1, len(wl.streams))
-    value = views_per_step_global * args.steps / (ms_value * 1e-3)
-    e2e = views_per_step_global * args.steps / (ms_e2e * 1e-3)
+    lanes_on = bool(args.priority_lanes) and n_streams > 1 and kind == "ours"
+
+    extras = {}
+    # ---- the isolated cost of the exchange (N > 1): what a step pays after its last backward
+    if ref_world > 1:
+        def xchg():
+            wl.flat.all_reduce()
+        ms_x = timed(xchg, 10, 3, device, ref_world) / 10
+        extras["exchange"] = {"kind": wl.flat.exchange_kind, "bytes": wl.flat.flat.numel() * 4, "ms": ms_x,
+                              "share_of_step": ms_x / ms_step,
+                              "note": "issued after the rank's last backward; nothing of the step is left to hide it"}
+    # ---- what an unmodified caller gets: every view on the caller's stream, no priority lanes
+    if kind == "ours" and not args.no_extras and n_streams > 1:
+        wl.set_streams(1, False)
+        v1, ms1, e1, mse1 = legs(wl, args, device, ref_world)
+        extras["value_single_stream"] = {"value": v1, "unit": "it/s", "ms_per_step": ms1,
+                                         "note": "drop-in: caller's stream only, src/mapper.py unchanged"}
+        extras["e2e_single_stream"] = {"value": e1, "unit": "it/s", "ms_per_step": mse1}
+    # ---- BASELINE config 4 proper: the FIXED window sharded over the ranks (strong scaling)
+    if kind == "ours" and not args.no_extras and ref_world > 1 and args.scaling == "weak" and args.workload == "replica":
+        ws = Workload(mod, args, device, wrank, ref_world, "strong", shared=wl, streams=args.streams)
+        sv, sms, se, smse = legs(ws, args, device, ref_world)
+        per_rank = -(-args.views // ref_world)
+        extras["strong"] = {"value": sv, "unit": "it/s", "ms_per_step": sms, "e2e": {"value": se, "ms_per_step": smse},
+                            "window_views_total": args.views, "max_views_per_rank": per_rank,
+                            "ceiling_speedup_vs_1gpu": args.views / per_rank,
+                            "note": "BASELINE config 4: one 10-keyframe window, views round-robin over the ranks"}
+        ws.streams.close()
+    if args.verify and kind == "ours":
+        wl.set_streams(args.streams, bool(args.priority_lanes))
+        extras["verify"] = verify_exchange(wl, args, device, wrank, ref_world)
 
     # ---- per-kernel durations (live CUDA events on the launching stream) and roofline of the dominant kernel
     roofline, stages, step_roof = None, None, None
@@ -352,11 +532,11 @@ def main():
     Pn = args.gaussians
     V = int((radii > 0).sum())
     N = wl.W * wl.H
+    M = args.sh_coeffs
     peak, peak_src = peaks()
     if kind == "ours":
         R = int(mod._PinnedInt.get(device).item())
-        from diff_gaussian_rasterization.window import ViewStreams
-        wl.streams = ViewStreams(device, 1)     # per-stage times are taken with the views back to back on one stream
+        wl.set_streams(1, False)     # per-stage times are taken with the views back to back on one stream
         _cabi.profile(True)
         _cabi.profile_read(reset=True)
         for _ in range(2):
@@ -368,27 +548,26 @@ def main():
         total = sum(stages.values())
         dom = max(stages, key=stages.get)
         alg = {"render_backward": 84 * R + 24 * N, "render_forward": 48 * R + 28 * N,
-               "radix_sort": 24 * R, "preprocess_forward": 44 * Pn + 79 * V, "preprocess_backward": 140 * Pn + 351 * V,
+               "tile_sort": 24 * R, "depth_sort_and_offsets": 24 * Pn,
+               "preprocess_forward": 44 * Pn + (67 + 12 * M) * V,
+               "preprocess_backward": (128 + 12 * M) * Pn + (327 + 24 * M) * V,
                "duplicate_with_keys": 8 * Pn + 12 * V + 12 * R, "ranges_and_records": 12 * R + 44 * R + 48 * R}
         a_bytes = alg.get(dom, 0)
         ach = a_bytes / (stages[dom] * 1e-3) / 1e9
-        # dram__bytes_read.sum + dram__bytes_write.sum per launch from the ncu --set full capture of this workload
-        # (profiles/r01_render_final_summary.md); only valid for the default scene
-        default_scene = (args.camera == CAMERA and args.gaussians == P_GAUSS)
-        traffic = {"render_backward": 248.1e6, "render_forward": 174.8e6}.get(dom) if default_scene else None
         roofline = {"kernel": dom, "bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
-                    "traffic": traffic, "algorithmic_bytes_per_launch": a_bytes, "ms_per_launch": stages[dom],
+                    "traffic": TRAFFIC.get(dom) if args.default_scene else None,
+                    "traffic_source": TRAFFIC["source"] if args.default_scene and dom in TRAFFIC else None,
+                    "algorithmic_bytes_per_launch": a_bytes, "ms_per_launch": stages[dom],
                     "share_of_kernel_time": stages[dom] / total, "peak_source": peak_src,
-                    "note": "render kernels reuse each 48-B record 256x; their limiter is FP32/SFU issue, shuffles and "
-                            "L2 atomics, not HBM (SURVEY.md §8d) — see profiles/"}
-    else:
-        R = None
-    if R is not None:
-        M = 1
+                    "note": "render kernels reuse each 48-B record 256x; their limiter is instruction issue (FP32/SFU, "
+                            "shared-memory wavefronts), not HBM (SURVEY.md §8d) — see profiles/"}
         b_alg = (244 + 12 * M) * Pn + (406 + 36 * M) * V + 172 * R + 52 * N
-        t_view = ms_value * 1e-3 / (args.steps * len(wl.view_ids))
+        t_view = ms_step * 1e-3 / len(wl.view_ids)
         step_roof = {"algorithmic_bytes_per_view": b_alg, "achieved_gbs": b_alg / t_view / 1e9,
                      "frac": b_alg / t_view / 1e9 / peak, "P": Pn, "V": V, "R": R, "N": N}
+
+    if rank == 0 and n_gpus == 1 and not args.no_extras and args.workload == "replica":
+        extras["configs"] = other_configs(mod, device)
 
     cb = None
     if rank == 0 and n_gpus == 1 and args.impl == "ours" and not args.no_cpu_baseline:
@@ -396,24 +575,26 @@ def main():
 
     if rank == 0:
         line = {
-            "metric": METRIC, "value": value, "unit": "it/s", "n_gpus": n_gpus, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": ms_value / args.steps, "higher_is_better": True,
+            "metric": args.metric, "value": value, "unit": "it/s", "n_gpus": n_gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True,
             "scaling": args.scaling, "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": f"{args.camera}_{wl.W}x{wl.H}_P{args.gaussians}_sh0_window{args.views}"
+            "config": {"workload": f"{args.camera}_{wl.W}x{wl.H}_P{args.gaussians}_sh{args.sh_degree}_window{args.views}"
                                    + ("_per_gpu" if args.scaling == "weak" else "_total"),
                        "views_per_step_global": views_per_step_global, "views_per_rank": len(wl.view_ids),
                        "it": "one view forward+backward with pose gradients",
-                       "collective": "all_reduce(sum,fp32) of the flat Gaussian-gradient buffer, "
-                                     f"{wl.flat.flat.numel() * 4} B/step" if ref_world > 1 else "none (1 GPU)",
-                       "l2": "inputs larger than L2: ~0.4 GB of state per view, 10 distinct views per step",
+                       "collective": (f"{wl.flat.exchange_kind} all-reduce (sum, fp32) of the flat Gaussian-gradient "
+                                      f"buffer, {wl.flat.flat.numel() * 4} B/step") if ref_world > 1 else "none (1 GPU)",
+                       "l2": "inputs larger than L2: ~0.4 GB of state per view, distinct views per step",
                        "resident": "Gaussian parameters stay in HBM (model state)",
-                       "streams": n_streams,
-                       "priority_lanes": bool(args.priority_lanes) and n_streams > 1 and kind == "ours"},
+                       "e2e_result": "rendered images stay on the device (training op); the D2H read is the step's "
+                                     "scalar <image, upstream> plus the per-view instance counts",
+                       "streams": n_streams, "priority_lanes": lanes_on},
             "e2e": {"value": e2e, "unit": "it/s", "h2d_bytes_per_step": wl.h2d_bytes_per_step(),
-                    "d2h_bytes_per_step": wl.d2h_bytes_per_step(), "ms_per_step": ms_e2e / args.steps},
+                    "d2h_bytes_per_step": wl.d2h_bytes_per_step(), "ms_per_step": ms_step_e2e},
             "gpu_launches": int(launches0) if kind == "ours" else 0,
             "clocks": clocks,
         }
+        line.update(extras)
         if roofline:
             line["roofline"] = roofline
         if stages:

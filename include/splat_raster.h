@@ -107,7 +107,9 @@ int splat_raster_backward(
  * that only forwards the tensors it was given. For them this entry point keeps the scratch inside the library, in a
  * fixed device array of SPLAT_NOALLOC_MAX_GAUSSIANS * 12 floats (12 MiB per GPU, held from the moment the library
  * is loaded on that GPU until the process ends). It calls no cudaMalloc/cudaFree and no allocating library routine;
- * the caller still passes every input and output, exactly as for splat_raster_backward minus `grad_scratch`.
+ * the caller still passes every input and output, exactly as for splat_raster_backward minus `grad_scratch`
+ * (per-Gaussian outputs may be NULL when not wanted, e.g. all of them for pose-only tracking; dL_dtau_partial is
+ * always required).
  *
  *   - P above SPLAT_NOALLOC_MAX_GAUSSIANS is refused with SPLAT_ERR_CAPACITY before anything is launched; use
  *     splat_raster_backward with your own scratch for larger clouds.
@@ -236,6 +238,17 @@ int splat_raster_deform_points(int P, int K, const splat_raster_deform_keyframe*
                                const float* intrinsics, int W, int H, float* table, float* xyz, float* rotation,
                                float* scaling, void* stream);
 
+/* Gradient exchange of the view-sharded mapping window inside one NVSwitch node, in place, fp32 sum (SURVEY.md §8e;
+ * the reference is single-GPU: no counterpart). Every rank holds its copy of the flat gradient buffer in memory that
+ * all ranks have mapped; `buffers[r]` is rank r's copy as seen from THIS process (a peer pointer), `multicast` the
+ * NVSwitch multicast address of the same allocation. One launch per rank does reduce-scatter + all-gather: rank
+ * `rank` sums its 1/world slice over all copies and writes the total into every copy, so all ranks end up with
+ * bit-identical sums. `count` floats, a multiple of 4; pointers 16-byte aligned; world <= 8.
+ * The kernel never waits for another GPU: the CALLER orders it between two cross-rank barriers on `stream` (before:
+ * every rank's gradients are complete; after: every slice has landed everywhere). */
+int splat_raster_allreduce_peer(float* const* buffers, int world, int rank, size_t count, void* stream);
+int splat_raster_allreduce_multimem(float* multicast, int world, int rank, size_t count, void* stream);
+
 /* Scheduling option, off by default: run the short latency-bound kernels of a forward (everything except the two
  * render kernels) on a highest-priority side stream, ordered against the caller's stream with events, so that with
  * several views in flight on different streams they are not queued behind another view's render CTAs.
@@ -262,6 +275,18 @@ int splat_raster_debug_views(int P, int R, int W, int H, void* geom, void* binni
 
 /* ---- diagnostics (measurement aids for bench.py; no counterpart in the reference, whose only aid is
  * debug=true -> cudaDeviceSynchronize after each stage, DGR/cuda_rasterizer/auxiliary.h:166-173) ---- */
+
+/* Debug mode, the equivalent of the reference's `debug` flag (CHECK_CUDA(..., debug), DGR/cuda_rasterizer/
+ * auxiliary.h:166-173: cudaDeviceSynchronize after every stage, throw with the place of the failure). While enabled,
+ * every stage of splat_raster_forward_preprocess / _forward_render / _backward is followed by a wait for its stream and
+ * an error check; the first failing stage ends the call, which returns the CUDA error code, and
+ * splat_raster_last_failed_stage() names the stage (per host thread; "" if none; `reset` clears it).
+ * `fail_stage` >= 0 (an index into splat_raster_stage_name) makes that stage REPORT a failure without faulting
+ * anything on the device: a hook for testing the caller's error path. Pass -1 otherwise. Library-wide switch;
+ * returns the previous setting. splat_raster_debug_sync_count counts the per-stage waits done so far. */
+int splat_raster_set_debug(int enable, int fail_stage);
+const char* splat_raster_last_failed_stage(int reset);
+unsigned long long splat_raster_debug_sync_count(int reset);
 
 /* Number of kernels this library has launched in this process (optionally reset). */
 unsigned long long splat_raster_launch_count(int reset);

@@ -3,6 +3,7 @@
 #include "common.cuh"
 #include "kernels.h"
 
+#include <atomic>
 #include <cmath>
 #include <map>
 #include <mutex>
@@ -86,7 +87,7 @@ enum Stage { ST_PREPROCESS = 0, ST_SCAN, ST_DUP, ST_SORT, ST_RECORDS, ST_RENDER_
 const char* kStageNames[ST_COUNT] = {"preprocess_forward", "depth_sort_and_offsets", "duplicate_with_keys",
                                      "tile_sort", "ranges_and_records", "render_forward", "zero_grad_scratch",
                                      "render_backward", "preprocess_backward"};
-unsigned long long g_launches = 0;
+std::atomic<unsigned long long> g_launches{0};
 int g_prof = 0;
 bool profiling_enabled() { return g_prof != 0; }
 int g_prof_dev = -1;
@@ -119,12 +120,33 @@ void prof_begin(int st, cudaStream_t s) {
     prof_harvest(st);
     cudaEventRecord(g_ev[st][0], s);
 }
-void prof_end(int st, cudaStream_t s, int kernels) {
+// ---- debug mode: the reference's CHECK_CUDA(..., debug) (DGR/cuda_rasterizer/auxiliary.h:166-173) synchronises after
+// every stage and throws with the place of the failure. Here: wait for the stage's stream, pick up any error, remember
+// which stage it was; the status goes back to the caller, who raises.
+int g_debug = 0;
+int g_debug_fail_stage = -1;                 // test hook: this stage reports a failure (nothing faults on the device)
+std::atomic<unsigned long long> g_debug_syncs{0};
+thread_local int t_failed_stage = -1;
+
+int prof_end(int st, cudaStream_t s, int kernels) {
     g_launches += (unsigned long long)kernels;
-    if (!g_prof) return;
-    cudaEventRecord(g_ev[st][1], s);
-    g_pending[st] = true;
+    if (g_prof) {
+        cudaEventRecord(g_ev[st][1], s);
+        g_pending[st] = true;
+    }
+    if (!g_debug) return SPLAT_OK;
+    cudaError_t e = cudaStreamSynchronize(s);
+    g_debug_syncs += 1;
+    if (e == cudaSuccess) e = cudaGetLastError();
+    if (e == cudaSuccess && g_debug_fail_stage == st) e = cudaErrorUnknown;
+    if (e != cudaSuccess) t_failed_stage = st;
+    return (int)e;
 }
+#define SPLAT_STAGE_END(st, s, kernels)              \
+    do {                                             \
+        const int rc__ = prof_end((st), (s), (kernels)); \
+        if (rc__ != SPLAT_OK) return rc__;           \
+    } while (0)
 }  // namespace
 
 extern "C" {
@@ -188,7 +210,7 @@ int splat_raster_forward_preprocess(int P, int D, int M, int W, int H, const flo
     cudaMemsetAsync(g.num_rendered, 0, 4 * sizeof(uint32_t), s);     // word 1: instance total summed by preprocess
     prof_begin(ST_PREPROCESS, s);
     launch_preprocess_forward(p, g, s);
-    prof_end(ST_PREPROCESS, s, 1);
+    SPLAT_STAGE_END(ST_PREPROCESS, s, 1);
     SPLAT_CUDA_CHECK_LAUNCH();
     if (num_rendered_host) {
         // hand R to the host now; the depth sort below runs while the caller sizes its binning buffer
@@ -202,7 +224,7 @@ int splat_raster_forward_preprocess(int P, int D, int M, int W, int H, const flo
     }
     prof_begin(ST_SCAN, s);
     launch_depth_sort_and_offsets(P, g, s);   // 2 histogram kernels + 4 sort passes + block sums + scan
-    prof_end(ST_SCAN, s, 8);
+    SPLAT_STAGE_END(ST_SCAN, s, 8);
     lane_end(caller, s);
     SPLAT_CUDA_CHECK_LAUNCH();
     return SPLAT_OK;
@@ -211,6 +233,23 @@ int splat_raster_forward_preprocess(int P, int D, int M, int W, int H, const flo
 int splat_raster_priority_lanes(int enable) {
     const int was = g_priority_lanes;
     if (enable >= 0) g_priority_lanes = enable ? 1 : 0;
+    if (enable == 0) {
+        // Switching the lanes off also releases them: one side stream and two events per (device, caller stream) that
+        // ever ran a forward. Work still queued on a destroyed stream or event completes first (CUDA defers the release).
+        std::lock_guard<std::mutex> lock(g_lane_mutex);
+        int cur = 0;
+        cudaGetDevice(&cur);
+        for (auto& kv : g_lanes) {
+            Lane& l = kv.second;
+            if (!l.hp) continue;
+            cudaSetDevice(kv.first.first);
+            cudaStreamDestroy(l.hp);
+            cudaEventDestroy(l.fork);
+            cudaEventDestroy(l.join);
+        }
+        g_lanes.clear();
+        cudaSetDevice(cur);
+    }
     return was;
 }
 
@@ -244,24 +283,24 @@ int splat_raster_forward_render(int P, int R, int W, int H, const float* backgro
         uint32_t* v1 = (passes & 1) ? b.point_list : b.vals_alt;
         prof_begin(ST_DUP, s);
         launch_duplicate_with_keys(P, gx, gy, radii, g, k0, v0, s);
-        prof_end(ST_DUP, s, 1);
+        SPLAT_STAGE_END(ST_DUP, s, 1);
         SPLAT_CUDA_CHECK_LAUNCH();
         prof_begin(ST_SORT, s);
         launch_sort_pairs(k0, v0, k1, v1, R, passes, b.sort_scratch, s);
-        prof_end(ST_SORT, s, passes + 2);
+        SPLAT_STAGE_END(ST_SORT, s, passes + 2);
         SPLAT_CUDA_CHECK_LAUNCH();
     }
     (void)colors_precomp;   // colours were folded into the per-Gaussian record by the preprocess kernel
     prof_begin(ST_RECORDS, s);
     launch_ranges_and_records(R, gx * gy, g, b, im.ranges, s);
-    prof_end(ST_RECORDS, s, R > 0 ? 1 : 0);
+    SPLAT_STAGE_END(ST_RECORDS, s, R > 0 ? 1 : 0);
     lane_end(caller, s);
     s = caller;
     SPLAT_CUDA_CHECK_LAUNCH();
     prof_begin(ST_RENDER_FWD, s);
     launch_render_forward(W, H, gx, gy, im.ranges, b.records, background, im.final_T, im.n_contrib, out_color,
                           out_depth, out_opacity, n_touched, s);
-    prof_end(ST_RENDER_FWD, s, 1);
+    SPLAT_STAGE_END(ST_RENDER_FWD, s, 1);
     SPLAT_CUDA_CHECK_LAUNCH();
     return SPLAT_OK;
 }
@@ -290,13 +329,13 @@ int splat_raster_backward(int P, int D, int M, int R, int W, int H, const float*
     ImageState im = ImageState::carve(image, (size_t)W * H, (size_t)gx * gy, nullptr);
     prof_begin(ST_ZERO, s);
     cudaError_t e = cudaMemsetAsync(grad_scratch, 0, sizeof(float) * SPLAT_GRAD_FLOATS * (size_t)P, s);
-    prof_end(ST_ZERO, s, 0);
+    SPLAT_STAGE_END(ST_ZERO, s, 0);
     if (e != cudaSuccess) return (int)e;
     if (R > 0) {
         prof_begin(ST_RENDER_BWD, s);
         launch_render_backward(W, H, gx, gy, im.ranges, b.records, background, im.final_T, im.n_contrib, dL_dout_color,
                                dL_dout_depth, grad_scratch, s);
-        prof_end(ST_RENDER_BWD, s, 1);
+        SPLAT_STAGE_END(ST_RENDER_BWD, s, 1);
         SPLAT_CUDA_CHECK_LAUNCH();
     }
     BwdParams p;
@@ -313,7 +352,7 @@ int splat_raster_backward(int P, int D, int M, int R, int W, int H, const float*
     p.dL_dtau = dL_dtau_partial;
     prof_begin(ST_PREPROCESS_BWD, s);
     launch_preprocess_backward(p, g, s);
-    prof_end(ST_PREPROCESS_BWD, s, 1);
+    SPLAT_STAGE_END(ST_PREPROCESS_BWD, s, 1);
     SPLAT_CUDA_CHECK_LAUNCH();
     return SPLAT_OK;
 }
@@ -470,6 +509,28 @@ int splat_raster_deform_points(int P, int K, const splat_raster_deform_keyframe*
     return SPLAT_OK;
 }
 
+int splat_raster_allreduce_peer(float* const* buffers, int world, int rank, size_t count, void* stream) {
+    if (!buffers || world < 1 || rank < 0 || rank >= world || (count & 3u) != 0) return SPLAT_ERR_ARG;
+    if (world > kMaxPeerRanks) return SPLAT_ERR_SIZE;
+    for (int r = 0; r < world; ++r)
+        if (!buffers[r] || (reinterpret_cast<uintptr_t>(buffers[r]) & 15u) != 0) return SPLAT_ERR_ARG;
+    if (world == 1 || count == 0) return SPLAT_OK;
+    const int k = launch_allreduce_peer(buffers, world, rank, count, (cudaStream_t)stream);
+    if (k < 0) return SPLAT_ERR_SIZE;
+    g_launches += (unsigned long long)k;
+    SPLAT_CUDA_CHECK_LAUNCH();
+    return SPLAT_OK;
+}
+
+int splat_raster_allreduce_multimem(float* multicast, int world, int rank, size_t count, void* stream) {
+    if (!multicast || world < 1 || rank < 0 || rank >= world || (count & 3u) != 0) return SPLAT_ERR_ARG;
+    if ((reinterpret_cast<uintptr_t>(multicast) & 15u) != 0) return SPLAT_ERR_ARG;
+    if (world == 1 || count == 0) return SPLAT_OK;
+    g_launches += (unsigned long long)launch_allreduce_multimem(multicast, world, rank, count, (cudaStream_t)stream);
+    SPLAT_CUDA_CHECK_LAUNCH();
+    return SPLAT_OK;
+}
+
 int splat_raster_debug_views(int P, int R, int W, int H, void* geom, void* binning, void* image,
                              splat_raster_views* out) {
     if (!out || P < 0 || R < 0 || W <= 0 || H <= 0) return SPLAT_ERR_ARG;
@@ -520,12 +581,14 @@ int splat_raster_backward_noalloc(int P, int D, int M, int R, int W, int H, cons
     if (P < 0 || R < 0 || W <= 0 || H <= 0 || D < 0 || D > 3) return SPLAT_ERR_SIZE;
     if (P > SPLAT_NOALLOC_MAX_GAUSSIANS) return SPLAT_ERR_CAPACITY;   // would not fit the built-in scratch
     if (P == 0) return SPLAT_OK;
+    // same contract as splat_raster_backward: a NULL per-Gaussian output means "not wanted" (pose-only tracking passes
+    // NULL for all of them); only the pose partials are mandatory
     if (!geom || !binning || !image || !background || !means3D || !radii || !viewmatrix || !projmatrix ||
-        !projmatrix_raw || !dL_dout_color || !dL_dout_depth || !dL_dmeans2D || !dL_dcolors || !dL_dopacity ||
-        !dL_dmeans3D || !dL_dcov3D || !dL_dtau_partial)
+        !projmatrix_raw || !dL_dout_color || !dL_dout_depth || !dL_dtau_partial)
         return SPLAT_ERR_ARG;
-    if (shs && (!dL_dsh || !campos)) return SPLAT_ERR_ARG;
-    if (scales && (!rotations || !dL_dscales || !dL_drotations)) return SPLAT_ERR_ARG;
+    if (shs && !campos) return SPLAT_ERR_ARG;
+    if (shs && D > 0 && !dL_dsh) return SPLAT_ERR_ARG;        // the SH direction term also feeds the pose gradient
+    if (scales && (!rotations || ((dL_dscales == nullptr) != (dL_drotations == nullptr)))) return SPLAT_ERR_ARG;
 
     // One-time set-up per device, done by the first call made with that device current: ask the runtime where this
     // device's copy of the array is. (Keep that first call outside of any stream capture.)
@@ -575,9 +638,24 @@ int splat_raster_backward_noalloc(int P, int D, int M, int R, int W, int H, cons
 }
 
 unsigned long long splat_raster_launch_count(int reset) {
-    const unsigned long long v = g_launches;
-    if (reset) g_launches = 0;
-    return v;
+    return reset ? g_launches.exchange(0) : g_launches.load();
+}
+
+int splat_raster_set_debug(int enable, int fail_stage) {
+    const int was = g_debug;
+    g_debug = enable ? 1 : 0;
+    g_debug_fail_stage = enable ? fail_stage : -1;
+    return was;
+}
+
+const char* splat_raster_last_failed_stage(int reset) {
+    const int st = t_failed_stage;
+    if (reset) t_failed_stage = -1;
+    return (st >= 0 && st < ST_COUNT) ? kStageNames[st] : "";
+}
+
+unsigned long long splat_raster_debug_sync_count(int reset) {
+    return reset ? g_debug_syncs.exchange(0) : g_debug_syncs.load();
 }
 
 int splat_raster_profile(int enable) {

@@ -79,6 +79,10 @@ void launch_activations_forward(int P, const float* raw_scaling, const float* ra
 void launch_activations_backward(int P, const float* raw_scaling, const float* raw_rotation, const float* raw_opacity,
                                  const float* g_scales, const float* g_rotations, const float* g_opacities,
                                  float* d_scaling, float* d_rotation, float* d_opacity, cudaStream_t s);
+// allreduce.cu
+constexpr int kMaxPeerRanks = 8;          // GPUs of one NVSwitch node
+int launch_allreduce_peer(float* const* buffers, int world, int rank, size_t count, cudaStream_t s);      // -> launches, < 0 unsupported
+int launch_allreduce_multimem(float* multicast, int world, int rank, size_t count, cudaStream_t s);       // -> launches
 // render.cu
 void launch_render_forward(int W, int H, int grid_x, int grid_y, const uint2* ranges, const float* records,
                            const float* bg, float* final_T, uint32_t* n_contrib, float* out_color, float* out_depth,

@@ -366,17 +366,28 @@ preprocess_backward_kernel(BwdParams p, GeomState g, float* __restrict__ tau_par
 void launch_preprocess_backward(const BwdParams& p, const GeomState& g, cudaStream_t s) {
     const int nblk = (p.P + kPreBlock - 1) / kPreBlock;
     // stage the SH rows through shared memory when they are longer than one coefficient (see the kernel)
-    const int stage_sh = (p.shs != nullptr && p.dL_dsh != nullptr && p.M > 1) ? 1 : 0;
-    const size_t smem = stage_sh ? sizeof(float) * (size_t)kPreBlock * sh_stage_stride(p.M) : 0;
-    if (smem > 48 * 1024) {
-        static bool raised[64] = {};     // opt in once per device to more than 48 KB of dynamic shared memory
+    int stage_sh = (p.shs != nullptr && p.dL_dsh != nullptr && p.M > 1) ? 1 : 0;
+    size_t smem = stage_sh ? sizeof(float) * (size_t)kPreBlock * sh_stage_stride(p.M) : 0;
+    constexpr size_t kOptIn = 64 * 1024;   // enough for M <= 21 coefficients (degree 3 has 16)
+    if (smem > 48 * 1024 && smem <= kOptIn) {
+        static int raised[64] = {};        // per device: 1 = opted in to kOptIn of dynamic shared memory, -1 = refused
         int dev = 0;
         cudaGetDevice(&dev);
-        if (dev >= 0 && dev < 64 && !raised[dev]) {
-            cudaFuncSetAttribute(preprocess_backward_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
-            cudaFuncSetAttribute(preprocess_backward_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
-            raised[dev] = true;
+        if (dev >= 0 && dev < 64 && raised[dev] == 0) {
+            const cudaError_t e1 = cudaFuncSetAttribute(preprocess_backward_kernel<true>,
+                                                        cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kOptIn);
+            const cudaError_t e2 = cudaFuncSetAttribute(preprocess_backward_kernel<false>,
+                                                        cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kOptIn);
+            raised[dev] = (e1 == cudaSuccess && e2 == cudaSuccess) ? 1 : -1;
+            if (raised[dev] < 0) cudaGetLastError();   // handled below, not an error of this call
         }
+        if (dev < 0 || dev >= 64 || raised[dev] < 0) smem = kOptIn + 1;
+    }
+    if (smem > kOptIn) {
+        // a padded SH layout with more rows than the staging buffer can hold (or no opt-in): every thread stores its
+        // own row directly, slower but correct for any M
+        stage_sh = 0;
+        smem = 0;
     }
     if (p.shs != nullptr && p.D > 0)
         preprocess_backward_kernel<true><<<nblk, kPreBlock, smem, s>>>(p, g, p.dL_dtau, stage_sh);

@@ -112,23 +112,31 @@ def _forward_impl(S, means3D, sh, colors_precomp, opacities, scales, rotations, 
         campos = _cabi.require_cuda("campos", S.campos)
         host_R = _PinnedInt.get(dev)
         rendered = 0
-        if P != 0:
-            _cabi.check(L.splat_raster_forward_preprocess(
-                P, int(S.sh_degree), M, W, H, _cabi.ptr(means3D), _cabi.ptr(scales), float(S.scale_modifier),
-                _cabi.ptr(rotations), _cabi.ptr(opacities), _cabi.ptr(sh), _cabi.ptr(cov3Ds_precomp),
-                _cabi.ptr(colors_precomp), _cabi.ptr(view), _cabi.ptr(proj), _cabi.ptr(campos), float(S.tanfovx),
-                float(S.tanfovy), int(bool(S.prefiltered)), radii.data_ptr(), n_touched.data_ptr(), geom.data_ptr(),
-                host_R.data_ptr(), stream), "forward_preprocess")
-            _cabi.check(L.splat_raster_forward_wait(), "forward_wait")    # returns while the depth sort still runs
-            rendered = int(host_R.item())
-        binning = torch.empty((L.splat_raster_binning_bytes(rendered),), dtype=torch.uint8, device=dev)
-        _cabi.check(L.splat_raster_forward_render(
-            P, rendered, W, H, _cabi.ptr(bg), _cabi.ptr(colors_precomp), _cabi.ptr(radii), geom.data_ptr(),
-            binning.data_ptr(), image.data_ptr(), out_color.data_ptr(), out_depth.data_ptr(), out_opacity.data_ptr(),
-            _cabi.ptr(n_touched), stream), "forward_render")
-        if S.debug:
-            torch.cuda.synchronize(dev)
+        # debug: wait and check after EVERY stage inside the library (the reference's CHECK_CUDA(..., debug),
+        # DGR/cuda_rasterizer/auxiliary.h:166-173); a failure names its stage in the exception
+        was_debug = _cabi.set_debug(True, _debug_fail_stage) if S.debug else None
+        try:
+            if P != 0:
+                _cabi.check(L.splat_raster_forward_preprocess(
+                    P, int(S.sh_degree), M, W, H, _cabi.ptr(means3D), _cabi.ptr(scales), float(S.scale_modifier),
+                    _cabi.ptr(rotations), _cabi.ptr(opacities), _cabi.ptr(sh), _cabi.ptr(cov3Ds_precomp),
+                    _cabi.ptr(colors_precomp), _cabi.ptr(view), _cabi.ptr(proj), _cabi.ptr(campos), float(S.tanfovx),
+                    float(S.tanfovy), int(bool(S.prefiltered)), radii.data_ptr(), n_touched.data_ptr(),
+                    geom.data_ptr(), host_R.data_ptr(), stream), "forward_preprocess")
+                _cabi.check(L.splat_raster_forward_wait(), "forward_wait")   # returns while the depth sort still runs
+                rendered = int(host_R.item())
+            binning = torch.empty((L.splat_raster_binning_bytes(rendered),), dtype=torch.uint8, device=dev)
+            _cabi.check(L.splat_raster_forward_render(
+                P, rendered, W, H, _cabi.ptr(bg), _cabi.ptr(colors_precomp), _cabi.ptr(radii), geom.data_ptr(),
+                binning.data_ptr(), image.data_ptr(), out_color.data_ptr(), out_depth.data_ptr(),
+                out_opacity.data_ptr(), _cabi.ptr(n_touched), stream), "forward_render")
+        finally:
+            if was_debug is not None:
+                _cabi.set_debug(was_debug)
     return rendered, out_color, radii, geom, binning, image, out_depth, out_opacity, n_touched
+
+
+_debug_fail_stage = -1      # tests set this to a stage index to exercise the error path of debug=True
 
 
 ALL_GRADS = dict(means2D=True, colors=True, opacity=True, means3D=True, cov3D=True, sh=True, scale_rot=True)
@@ -172,24 +180,27 @@ def _backward_impl(S, means3D, radii, colors_precomp, scales, rotations, cov3Ds_
         if P != 0:
             gc = _cabi.require_cuda("grad_out_color", grad_out_color)
             gd = _cabi.require_cuda("grad_out_depth", grad_out_depth)
-            _cabi.check(L.splat_raster_backward(
-                P, int(S.sh_degree), M, int(num_rendered), W, H, _cabi.ptr(_cabi.require_cuda("bg", S.bg)),
-                _cabi.ptr(means3D), _cabi.ptr(sh), _cabi.ptr(colors_precomp), _cabi.ptr(scales),
-                float(S.scale_modifier), _cabi.ptr(rotations), _cabi.ptr(cov3Ds_precomp),
-                _cabi.ptr(_cabi.require_cuda("viewmatrix", S.viewmatrix)),
-                _cabi.ptr(_cabi.require_cuda("projmatrix", S.projmatrix)),
-                _cabi.ptr(_cabi.require_cuda("projmatrix_raw", S.projmatrix_raw)),
-                _cabi.ptr(_cabi.require_cuda("campos", S.campos)), float(S.tanfovx), float(S.tanfovy),
-                radii.data_ptr(), geom.data_ptr(), binning.data_ptr(), image.data_ptr(), gc.data_ptr(), gd.data_ptr(),
-                scratch.data_ptr(), _cabi.ptr(dL_dmeans2D), _cabi.ptr(dL_dcolors), _cabi.ptr(dL_dopacity),
-                _cabi.ptr(dL_dmeans3D), _cabi.ptr(dL_dcov3D), _cabi.ptr(dL_dsh),
-                _cabi.ptr(dL_dscales) if has_scale else None, _cabi.ptr(dL_drotations) if has_scale else None,
-                tau_partial.data_ptr(), stream), "backward")
+            was_debug = _cabi.set_debug(True, _debug_fail_stage) if S.debug else None
+            try:
+                _cabi.check(L.splat_raster_backward(
+                    P, int(S.sh_degree), M, int(num_rendered), W, H, _cabi.ptr(_cabi.require_cuda("bg", S.bg)),
+                    _cabi.ptr(means3D), _cabi.ptr(sh), _cabi.ptr(colors_precomp), _cabi.ptr(scales),
+                    float(S.scale_modifier), _cabi.ptr(rotations), _cabi.ptr(cov3Ds_precomp),
+                    _cabi.ptr(_cabi.require_cuda("viewmatrix", S.viewmatrix)),
+                    _cabi.ptr(_cabi.require_cuda("projmatrix", S.projmatrix)),
+                    _cabi.ptr(_cabi.require_cuda("projmatrix_raw", S.projmatrix_raw)),
+                    _cabi.ptr(_cabi.require_cuda("campos", S.campos)), float(S.tanfovx), float(S.tanfovy),
+                    radii.data_ptr(), geom.data_ptr(), binning.data_ptr(), image.data_ptr(), gc.data_ptr(), gd.data_ptr(),
+                    scratch.data_ptr(), _cabi.ptr(dL_dmeans2D), _cabi.ptr(dL_dcolors), _cabi.ptr(dL_dopacity),
+                    _cabi.ptr(dL_dmeans3D), _cabi.ptr(dL_dcov3D), _cabi.ptr(dL_dsh),
+                    _cabi.ptr(dL_dscales) if has_scale else None, _cabi.ptr(dL_drotations) if has_scale else None,
+                    tau_partial.data_ptr(), stream), "backward")
+            finally:
+                if was_debug is not None:
+                    _cabi.set_debug(was_debug)
             grad_tau = tau_partial.sum(dim=0)
         else:
             grad_tau = torch.zeros(6, **f32)
-        if S.debug:
-            torch.cuda.synchronize(dev)
     return dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations, grad_tau
 
 
@@ -197,6 +208,17 @@ class _RasterizeGaussians(torch.autograd.Function):
     @staticmethod
     def forward(ctx, means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp, theta, rho,
                 raster_settings):
+        # Dense fp32 copies are made HERE (the reference calls .contiguous().data<float>() in both directions,
+        # DGR/rasterize_points.cu) and the same tensors are saved for backward: an expanded / sliced / fp16 input is
+        # then read with the right strides by both passes.
+        def dense(name, t):
+            return _cabi.require_cuda(name, t) if t.numel() != 0 else t
+        if means3D.ndimension() != 2 or means3D.size(1) != 3:
+            raise RuntimeError("means3D must have dimensions (num_points, 3)")
+        means3D = _cabi.require_cuda("means3D", means3D)
+        sh, colors_precomp = dense("sh", sh), dense("colors_precomp", colors_precomp)
+        opacities, scales, rotations = dense("opacities", opacities), dense("scales", scales), dense("rotations", rotations)
+        cov3Ds_precomp = dense("cov3Ds_precomp", cov3Ds_precomp)
         args = (raster_settings, means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp)
         if raster_settings.debug:
             cpu_args = cpu_deep_copy_tuple(args[1:])  # copy them before they can be corrupted

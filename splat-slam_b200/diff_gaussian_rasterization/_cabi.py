@@ -37,6 +37,8 @@ EXPORTS = (
     "splat_raster_densify_stats", "splat_raster_visibility_count",
     "splat_raster_knn_scratch_bytes", "splat_raster_knn_mean_dist2",
     "splat_raster_deform_points", "splat_raster_activations_forward", "splat_raster_activations_backward", "splat_raster_priority_lanes",
+    "splat_raster_backward_noalloc", "splat_raster_set_debug", "splat_raster_last_failed_stage",
+    "splat_raster_debug_sync_count", "splat_raster_allreduce_peer", "splat_raster_allreduce_multimem",
 )
 
 
@@ -79,6 +81,16 @@ def lib() -> ctypes.CDLL:
     L.splat_raster_stage_name.argtypes = [c_int]
     L.splat_raster_profile_read.restype = c_int
     L.splat_raster_profile_read.argtypes = [POINTER(c_float), POINTER(c_int), c_int]
+    L.splat_raster_set_debug.restype = c_int
+    L.splat_raster_set_debug.argtypes = [c_int, c_int]
+    L.splat_raster_last_failed_stage.restype = ctypes.c_char_p
+    L.splat_raster_last_failed_stage.argtypes = [c_int]
+    L.splat_raster_debug_sync_count.restype = ctypes.c_ulonglong
+    L.splat_raster_debug_sync_count.argtypes = [c_int]
+    L.splat_raster_allreduce_peer.restype = c_int
+    L.splat_raster_allreduce_peer.argtypes = [POINTER(c_void_p), c_int, c_int, c_size_t, P]
+    L.splat_raster_allreduce_multimem.restype = c_int
+    L.splat_raster_allreduce_multimem.argtypes = [P, c_int, c_int, c_size_t, P]
     if L.splat_raster_abi_version() != ABI_VERSION:
         raise SplatRasterError("libsplat_raster.so ABI version mismatch; rebuild")
     _lib = L
@@ -89,7 +101,10 @@ def check(status: int, what: str) -> None:
     if status == 0:
         return
     if status > 0:
-        raise SplatRasterError(f"{what}: CUDA error {status} ({torch.cuda.get_device_name() if torch.cuda.is_available() else 'no device'})")
+        stage = lib().splat_raster_last_failed_stage(1).decode()
+        where = f" in stage '{stage}'" if stage else ""
+        raise SplatRasterError(f"{what}: CUDA error {status}{where} "
+                               f"({torch.cuda.get_device_name() if torch.cuda.is_available() else 'no device'})")
     raise SplatRasterError(f"{what}: invalid argument (code {status})")
 
 
@@ -150,6 +165,21 @@ def priority_lanes(enable: bool | None = None) -> bool:
     L.splat_raster_priority_lanes.restype = c_int
     L.splat_raster_priority_lanes.argtypes = [c_int]
     return bool(L.splat_raster_priority_lanes(-1 if enable is None else int(bool(enable))))
+
+
+def set_debug(enable: bool, fail_stage: int = -1) -> bool:
+    """Per-stage synchronisation and error check, the reference's `debug` (see include/splat_raster.h)."""
+    return bool(lib().splat_raster_set_debug(1 if enable else 0, int(fail_stage)))
+
+
+def stage_index(name: str) -> int:
+    L = lib()
+    names = [L.splat_raster_stage_name(i).decode() for i in range(L.splat_raster_stage_count())]
+    return names.index(name)
+
+
+def debug_sync_count(reset: bool = False) -> int:
+    return int(lib().splat_raster_debug_sync_count(1 if reset else 0))
 
 
 def launch_count(reset: bool = False) -> int:

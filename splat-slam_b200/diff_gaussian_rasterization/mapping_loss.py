@@ -4,8 +4,8 @@ Mirrors `get_loss_mapping(config, image, depth, viewpoint, opacity, initializati
 (thirdparty/monogs/utils/slam_utils.py:71-105, the `ssim_loss: False` path that configs/splat_slam.yaml:36 selects):
 same arguments, same value, same gradients w.r.t. `image`, `depth`, `viewpoint.exposure_a`, `viewpoint.exposure_b`,
 but one kernel instead of ~10 elementwise/reduction kernels, and the ground-truth depth is uploaded once per
-viewpoint instead of on every call (the reference does `torch.from_numpy(viewpoint.depth).to(device)` each time,
-slam_utils.py:87-89). No CPU path.
+`viewpoint.depth` array instead of on every call (the reference does `torch.from_numpy(viewpoint.depth).to(device)`
+each time, slam_utils.py:87-89; see `_device_depth` for when it is uploaded again). No CPU path.
 """
 from __future__ import annotations
 
@@ -91,6 +91,32 @@ def fused_mapping_loss(image, depth, exposure_a, exposure_b, gt_image, gt_depth,
                                    rgb_boundary_threshold, initialization)
 
 
+def _device_depth(viewpoint, device):
+    """Ground-truth depth of a viewpoint on the device, shape (1, H, W).
+
+    The reference uploads `viewpoint.depth` (a numpy array) on every call (slam_utils.py:87-89). Here the upload is
+    kept on the viewpoint and reused for as long as `viewpoint.depth` is THE SAME OBJECT: Splat-SLAM replaces the array
+    when it re-aligns a keyframe's depth (src/mapper.py:633-639 after bundle adjustment, :1040-1046 in final_refine), and
+    a replaced array is uploaded again. The cache holds a reference to the source array, so its identity cannot be
+    recycled. Code that edits the array in place after the first loss call must call `invalidate_depth_cache`."""
+    d = viewpoint.depth
+    cached = getattr(viewpoint, "_depth_cuda", None)
+    if cached is not None and cached[0] is d and cached[1].device == device:
+        return cached[1]
+    t = (torch.from_numpy(d) if not torch.is_tensor(d) else d).to(dtype=torch.float32, device=device)[None]
+    try:
+        viewpoint._depth_cuda = (d, t)
+    except Exception:
+        pass
+    return t
+
+
+def invalidate_depth_cache(viewpoint):
+    """Forget the uploaded ground-truth depth of `viewpoint` (needed only after an in-place edit of `viewpoint.depth`)."""
+    if getattr(viewpoint, "_depth_cuda", None) is not None:
+        viewpoint._depth_cuda = None
+
+
 def get_loss_mapping(config, image, depth, viewpoint, opacity, initialization=False):
     """Drop-in for thirdparty/monogs/utils/slam_utils.py:71-78 (+ get_loss_mapping_rgbd :81-105)."""
     training = config["Training"]
@@ -101,13 +127,6 @@ def get_loss_mapping(config, image, depth, viewpoint, opacity, initialization=Fa
     gt_image = viewpoint.original_image
     if not gt_image.is_cuda:
         gt_image = gt_image.cuda()
-    gt_depth = getattr(viewpoint, "_depth_cuda", None)
-    if gt_depth is None or gt_depth.device != image.device:
-        d = viewpoint.depth
-        gt_depth = (torch.from_numpy(d) if not torch.is_tensor(d) else d).to(dtype=torch.float32, device=image.device)[None]
-        try:
-            viewpoint._depth_cuda = gt_depth      # uploaded once per viewpoint, not once per call
-        except Exception:
-            pass
+    gt_depth = _device_depth(viewpoint, image.device)
     return fused_mapping_loss(image, depth, viewpoint.exposure_a, viewpoint.exposure_b, gt_image, gt_depth, alpha, thr,
                               initialization)

@@ -31,14 +31,33 @@ class FlatGrads:
     """One contiguous fp32 buffer holding the gradients of all Gaussian leaf parameters.
 
     The parameters' `.grad` fields are views into the buffer, so autograd accumulates the per-view gradients in
-    place and the buffer can be handed to a single all-reduce without packing."""
+    place and the buffer can be handed to a single exchange without packing.
 
-    def __init__(self, params: Dict[str, torch.Tensor]):
+    `exchange` picks how `all_reduce()` sums the buffer over the ranks of `group`:
+      "nccl"  `dist.all_reduce` (also what the gloo CPU tests use);
+      "peer"  this library's own kernel over NVLink peer memory: the buffer is allocated as torch symmetric memory, every
+              rank reduces its 1/world slice straight out of the other GPUs' buffers and writes the total back into all
+              of them (`splat_raster_allreduce_multimem` through the NVSwitch when the allocation has a multicast
+              address, else `splat_raster_allreduce_peer`), bracketed by two symmetric-memory barriers;
+      "auto"  "peer" when every rank managed to set it up (one node, CUDA, world <= 8), else "nccl"."""
+
+    def __init__(self, params: Dict[str, torch.Tensor], exchange: str = "nccl", group=None):
         self.names = [n for n in PARAM_ORDER if params.get(n) is not None]
         self.params = params
         total = sum(params[n].numel() for n in self.names)
         ref = params[self.names[0]]
-        self.flat = torch.zeros(total, dtype=torch.float32, device=ref.device)
+        self.group = group
+        self.exchange_kind = "nccl"
+        self._peer = None
+        padded = (total + 63) // 64 * 64          # whole 16-byte vectors for every rank's slice
+        store = None
+        if exchange in ("auto", "peer") and ref.is_cuda and dist.is_available() and dist.is_initialized() \
+                and dist.get_world_size(group) > 1:
+            store = self._try_symmetric(padded, ref.device, group, must=(exchange == "peer"))
+        if store is None:
+            store = torch.zeros(padded, dtype=torch.float32, device=ref.device)
+        self._store = store
+        self.flat = store[:total]
         off = 0
         self.views = {}
         for n in self.names:
@@ -48,6 +67,37 @@ class FlatGrads:
             self.views[n] = v
             off += p.numel()
 
+    def _try_symmetric(self, padded, device, group, must):
+        """Allocate the buffer as symmetric memory and exchange the peer pointers; every rank reports whether it
+        worked and the peer path is only used when all of them did (otherwise all fall back to NCCL together)."""
+        world = dist.get_world_size(group)
+        store, err = None, None
+        try:
+            if world > 8:
+                raise RuntimeError("peer exchange supports up to 8 ranks (one NVSwitch node)")
+            import torch.distributed._symmetric_memory as symm_mem
+            from . import _cabi
+            _cabi.lib()
+            store = symm_mem.empty(padded, dtype=torch.float32, device=device)
+            store.zero_()
+            hdl = symm_mem.rendezvous(store, group=(group if group is not None else dist.group.WORLD))
+            ptrs = [int(x) for x in hdl.buffer_ptrs]
+            mc = int(getattr(hdl, "multicast_ptr", 0) or 0)
+            if len(ptrs) != world:
+                raise RuntimeError("rendezvous returned %d buffers for %d ranks" % (len(ptrs), world))
+            self._peer = dict(hdl=hdl, ptrs=ptrs, mc=mc, world=world, rank=dist.get_rank(group), count=padded)
+        except Exception as ex:     # noqa: BLE001 - any failure means "use NCCL"
+            err, store, self._peer = ex, None, None
+        ok = torch.tensor([1 if self._peer is not None else 0], device=device, dtype=torch.int32)
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=group)
+        if int(ok.item()) != 1:
+            self._peer, store = None, None
+            if must:
+                raise RuntimeError(f"peer-memory gradient exchange unavailable: {err}")
+            return None
+        self.exchange_kind = "peer-multimem" if self._peer["mc"] else "peer"
+        return store
+
     def zero_(self):
         self.flat.zero_()
         for n in self.names:          # re-attach in case an optimizer replaced .grad
@@ -55,8 +105,26 @@ class FlatGrads:
                 self.params[n].grad = self.views[n]
 
     def all_reduce(self, group=None):
-        if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
+        group = group if group is not None else self.group
+        if not (dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1):
+            return
+        if self._peer is None:
             dist.all_reduce(self.flat, op=dist.ReduceOp.SUM, group=group)
+            return
+        import ctypes
+        from . import _cabi
+        pr = self._peer
+        L = _cabi.lib()
+        stream = _cabi.stream_ptr(self.flat.device)
+        pr["hdl"].barrier(channel=0)          # every rank's gradients are complete
+        if pr["mc"]:
+            _cabi.check(L.splat_raster_allreduce_multimem(pr["mc"], pr["world"], pr["rank"], pr["count"], stream),
+                        "allreduce_multimem")
+        else:
+            arr = (ctypes.c_void_p * pr["world"])(*pr["ptrs"])
+            _cabi.check(L.splat_raster_allreduce_peer(arr, pr["world"], pr["rank"], pr["count"], stream),
+                        "allreduce_peer")
+        pr["hdl"].barrier(channel=1)          # every rank's slice has landed in every buffer
 
 
 class ViewStreams:
@@ -71,13 +139,30 @@ class ViewStreams:
     def __init__(self, device, n: int = 5, priority_lanes: bool = True):
         self.device = torch.device(device)
         self.streams = [torch.cuda.Stream(device=self.device) for _ in range(n)] if n > 1 else []
+        self._restore = []          # process-wide switches this object flipped, undone by close()
         if self.streams:   # accumulation into the shared leaves deliberately crosses streams; autograd orders it
-            torch.autograd.graph.set_warn_on_accumulate_grad_stream_mismatch(False)
+            graph = torch.autograd.graph
+            if hasattr(graph, "set_warn_on_accumulate_grad_stream_mismatch"):      # recent torch only
+                graph.set_warn_on_accumulate_grad_stream_mismatch(False)    # advisory only; left off
             if priority_lanes:
                 # the ~20 short kernels of each forward go to a high-priority side stream so that they are not
                 # queued behind the render CTAs of the other views in flight (library-wide switch)
                 from . import _cabi
-                _cabi.priority_lanes(True)
+                was = _cabi.priority_lanes(True)
+                if not was:
+                    self._restore.append(lambda: _cabi.priority_lanes(False))   # also frees the library's side streams
+
+    def close(self):
+        """Undo the library-wide switch this object set (priority lanes; also frees the library's side streams)."""
+        while self._restore:
+            self._restore.pop()()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+        return False
 
     def __len__(self):
         return len(self.streams)

@@ -25,6 +25,8 @@ CASES = {
     "ragged_sh2": dict(camera="ragged", P=900, sh_coeffs=9, sh_degree=2, view_k=4, seed=2),
     "small_sh3": dict(camera="small", P=20000, sh_coeffs=16, sh_degree=3, view_k=1),
     "small_M16_D0": dict(camera="small", P=3000, sh_coeffs=16, sh_degree=0, view_k=5),
+    # padded SH layout with more rows than the per-Gaussian backward can stage in shared memory (M > 21)
+    "small_M25_D3": dict(camera="small", P=3000, sh_coeffs=25, sh_degree=3, view_k=3),
     "small_precomp": dict(camera="small", P=20000, use_colors_precomp=True, use_cov3d_precomp=True, view_k=3),
     "small_colors_only": dict(camera="small", P=4000, use_colors_precomp=True, view_k=6),
     "big_splats": dict(camera="small", P=5000, scale_modifier=1.7, sigma_px=6.0),
@@ -234,6 +236,86 @@ def test_pose_only_gradients():
     full = T.run_module(m, case)
     assert T.rel_err(theta.grad, full["grad_theta"]) < 1e-4 and T.rel_err(rho.grad, full["grad_rho"]) < 1e-4
     assert float(theta.grad.abs().max()) > 0
+
+
+def test_strided_and_expanded_inputs_are_read_densely_in_both_passes():
+    """Isotropic scales given as `s.expand(-1, 3)` and an SH tensor that is a strided slice: forward AND backward must see
+    the dense values. Checked against dense copies of the same inputs, run through this library and through the compiled
+    reference. (The reference itself only handles strided inputs in its forward: its backward takes `scales.data_ptr()`
+    and `rotations.data_ptr()` without `.contiguous()`, DGR/rasterize_points.cu:180-182, and reads an expanded tensor
+    out of bounds. That defect is not reproduced.)"""
+    m = T.load_ours()
+    case = T.make_case(camera="small", P=6000, sh_coeffs=4, sh_degree=1, view_k=2)
+    dev = "cuda"
+    iso = case["scales"][:, :1].contiguous()
+    sh_wide = torch.zeros(6000, 8, 3)
+    sh_wide[:, ::2] = case["shs"]
+
+    def run(mod, dense):
+        leaves = dict(means3D=case["means3D"].to(dev).requires_grad_(True), opacities=case["opacities"].to(dev).requires_grad_(True),
+                      rotations=case["rotations"].to(dev).requires_grad_(True), iso=iso.to(dev).requires_grad_(True),
+                      shw=sh_wide.to(dev).requires_grad_(True))
+        scales = leaves["iso"].expand(-1, 3)
+        shs = leaves["shw"][:, ::2]
+        if dense:
+            scales, shs = scales.contiguous(), shs.contiguous()
+        else:
+            assert not scales.is_contiguous() and not shs.is_contiguous()
+        color, radii, depth, opacity, n_touched = mod.GaussianRasterizer(T.settings_for(mod, case, dev))(
+            means3D=leaves["means3D"], means2D=torch.zeros(6000, 3, device=dev, requires_grad=True),
+            opacities=leaves["opacities"], shs=shs, scales=scales, rotations=leaves["rotations"],
+            theta=torch.zeros(3, device=dev, requires_grad=True), rho=torch.zeros(3, device=dev, requires_grad=True))
+        ((color * case["Wc"].to(dev)).sum() + (depth * case["Wd"].to(dev)).sum()).backward()
+        return color.detach(), {k: v.grad for k, v in leaves.items()}
+
+    c_ours, g_ours = run(m, dense=False)
+    checkers = [run(m, dense=True)]
+    if T.load_ref() is not None:
+        checkers.append(run(T.load_ref(), dense=True))
+    for c_ref, g_ref in checkers:
+        assert float((c_ours - c_ref).abs().max()) <= T.FWD_ATOL
+        for k in g_ref:
+            assert T.rel_err(g_ours[k], g_ref[k]) <= T.GRAD_RTOL, k
+    assert float(g_ours["iso"].abs().max()) > 0 and float(g_ours["shw"][:, 1::2].abs().max()) == 0.0
+
+
+def test_debug_mode_checks_every_stage_and_names_the_failing_one(tmp_path, monkeypatch):
+    """`debug=True` (DGR/cuda_rasterizer/auxiliary.h:166-173: synchronise and check after EACH stage, report where it
+    failed; DGR __init__.py:59-67,126-138: dump the inputs). The failure is injected through the library's test hook,
+    which makes a stage report an error without faulting the device."""
+    import diff_gaussian_rasterization as m
+    from diff_gaussian_rasterization import _cabi
+    monkeypatch.chdir(tmp_path)
+    case = T.make_case(camera="small", P=2000, view_k=1)
+    plain = T.run_module(m, case)
+    case_dbg = dict(case)
+    S = T.settings_for(m, case, "cuda")._replace(debug=True)
+    monkeypatch.setattr(T, "settings_for", lambda mod, c, device="cuda": S)
+    _cabi.debug_sync_count(reset=True)
+    dbg = T.run_module(m, case_dbg)
+    # forward: preprocess, depth sort, key emission, tile sort, records, render; backward: clear, render, per-Gaussian
+    assert _cabi.debug_sync_count(reset=True) == 9
+    assert not _cabi.set_debug(False), "debug mode must be switched off again after the call"
+    for k in ("color", "depth", "radii", "n_touched"):
+        assert torch.equal(plain[k], dbg[k]), k
+    assert T.rel_err(dbg["grad_means3D"], plain["grad_means3D"]) <= T.GRAD_RTOL
+    assert not os.path.exists("snapshot_fw.dump") and not os.path.exists("snapshot_bw.dump")
+    # a failing forward stage: named in the exception, inputs dumped
+    monkeypatch.setattr(m, "_debug_fail_stage", _cabi.stage_index("tile_sort"))
+    with pytest.raises(_cabi.SplatRasterError, match="tile_sort"):
+        T.run_module(m, case_dbg)
+    dump = torch.load("snapshot_fw.dump", weights_only=False)
+    assert torch.equal(dump[0], case["means3D"])
+    assert not _cabi.set_debug(False)
+    # a failing backward stage
+    monkeypatch.setattr(m, "_debug_fail_stage", _cabi.stage_index("render_backward"))
+    with pytest.raises(_cabi.SplatRasterError, match="render_backward"):
+        T.run_module(m, case_dbg)
+    assert os.path.exists("snapshot_bw.dump")
+    monkeypatch.setattr(m, "_debug_fail_stage", -1)
+    torch.cuda.synchronize()
+    again = T.run_module(m, case)      # the library is healthy afterwards
+    assert torch.equal(again["color"], plain["color"])
 
 
 def test_non_default_stream_and_repeatability():

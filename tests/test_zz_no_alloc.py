@@ -121,3 +121,19 @@ def test_noalloc_rejects_clouds_beyond_its_capacity():
         noalloc.backward_noalloc(*too_many, *[out[k] for k in OUT_NAMES], torch.cuda.current_stream().cuda_stream)
     torch.cuda.synchronize()
     assert all(bool((out[k] == 7.0).all()) for k in OUT_NAMES if out[k].numel()), "nothing may be launched"
+
+
+def test_noalloc_pose_only_call_passes_null_for_the_per_gaussian_outputs():
+    """A tracking loop only wants the pose gradient: every per-Gaussian output is NULL, as `splat_raster_backward`
+    allows; the pose partials must equal those of the full call."""
+    from diff_gaussian_rasterization import noalloc
+    case = T.make_case(camera="small", P=5000, view_k=2)
+    state = _forward_state(case)
+    P, M, head = _common_args(case, *state)
+    full = _run_noalloc(case, state, fill=float("nan"))
+    tau = torch.full(((P + 255) // 256, 6), float("nan"), device="cuda")
+    noalloc.backward_noalloc(*head, None, None, None, None, None, None, None, None, tau,
+                             torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize()
+    assert bool(torch.isfinite(tau).all())
+    assert T.rel_err(tau.sum(0), full["dL_dtau_partial"].sum(0)) <= T.GRAD_RTOL
