@@ -548,10 +548,10 @@ def main():
         total = sum(stages.values())
         dom = max(stages, key=stages.get)
         alg = {"render_backward": 84 * R + 24 * N, "render_forward": 48 * R + 28 * N,
-               "tile_sort": 24 * R, "depth_sort_and_offsets": 24 * Pn,
+               "tile_sort_records_ranges": 24 * R + 48 * R + 48 * R, "depth_sort_and_offsets": 24 * Pn,
                "preprocess_forward": 44 * Pn + (67 + 12 * M) * V,
                "preprocess_backward": (128 + 12 * M) * Pn + (327 + 24 * M) * V,
-               "duplicate_with_keys": 8 * Pn + 12 * V + 12 * R, "ranges_and_records": 12 * R + 44 * R + 48 * R}
+               "duplicate_with_keys": 8 * Pn + 12 * V + 12 * R}
         a_bytes = alg.get(dom, 0)
         ach = a_bytes / (stages[dom] * 1e-3) / 1e9
         roofline = {"kernel": dom, "bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,

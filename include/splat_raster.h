@@ -256,7 +256,11 @@ int splat_raster_allreduce_multimem(float* multicast, int world, int rank, size_
 int splat_raster_priority_lanes(int enable);
 
 /* Test/diagnostic view into the opaque buffers (device pointers into the caller's buffers; layout is private).
- * Mirrors what the parity harness carves out of the reference's buffers (rasterizer_impl.cu:155-194). */
+ * Mirrors what the parity harness carves out of the reference's buffers (rasterizer_impl.cu:155-194).
+ * `keys` and `point_list` (the reference's sorted 64-bit keys and point list) are not needed by the render kernels,
+ * which read per-instance records; a forward only materialises them while splat_raster_keep_sort_output is on
+ * (enable: 1 on, 0 off, < 0 query; returns the previous setting; library-wide, off by default). */
+int splat_raster_keep_sort_output(int enable);
 typedef struct splat_raster_views {
     const float* depths;              /* [P] */
     const float* means2D;             /* [P*2] */

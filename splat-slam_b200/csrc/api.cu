@@ -82,11 +82,12 @@ void lane_end(cudaStream_t s, cudaStream_t used) {
 }
 
 // ---- diagnostics: kernel-launch counter and optional per-stage CUDA-event timing ------------------------
-enum Stage { ST_PREPROCESS = 0, ST_SCAN, ST_DUP, ST_SORT, ST_RECORDS, ST_RENDER_FWD, ST_ZERO, ST_RENDER_BWD,
+enum Stage { ST_PREPROCESS = 0, ST_SCAN, ST_DUP, ST_SORT, ST_RENDER_FWD, ST_ZERO, ST_RENDER_BWD,
              ST_PREPROCESS_BWD, ST_COUNT };
 const char* kStageNames[ST_COUNT] = {"preprocess_forward", "depth_sort_and_offsets", "duplicate_with_keys",
-                                     "tile_sort", "ranges_and_records", "render_forward", "zero_grad_scratch",
+                                     "tile_sort_records_ranges", "render_forward", "zero_grad_scratch",
                                      "render_backward", "preprocess_backward"};
+int g_keep_sort_output = 0;
 std::atomic<unsigned long long> g_launches{0};
 int g_prof = 0;
 bool profiling_enabled() { return g_prof != 0; }
@@ -274,32 +275,33 @@ int splat_raster_forward_render(int P, int R, int W, int H, const float* backgro
     BinningState b = BinningState::carve(binning, (size_t)R, nullptr);
     ImageState im = ImageState::carve(image, (size_t)W * H, (size_t)gx * gy, nullptr);
     const int passes = tile_sort_passes(gx, gy);
+    if (R <= 0) launch_reset_ranges(gx * gy, im.ranges, s);     // otherwise preset by the key-emission kernel
     if (R > 0) {
-        // the ping-pong sort leaves its result in its first buffer pair for an even pass count and in the second
-        // for an odd one: emit the unsorted instances so that the result always lands in b.tkey / b.point_list
-        uint32_t* k0 = (passes & 1) ? b.tkey_alt : b.tkey;
-        uint32_t* v0 = (passes & 1) ? b.vals_alt : b.point_list;
-        uint32_t* k1 = (passes & 1) ? b.tkey : b.tkey_alt;
-        uint32_t* v1 = (passes & 1) ? b.point_list : b.vals_alt;
+        // the ping-pong sort reads its input from the first buffer pair; the last pass writes records, not pairs
         prof_begin(ST_DUP, s);
-        launch_duplicate_with_keys(P, gx, gy, radii, g, k0, v0, s);
+        launch_duplicate_with_keys(P, gx, gy, radii, g, b.tkey, b.point_list, im.ranges, s);
         SPLAT_STAGE_END(ST_DUP, s, 1);
         SPLAT_CUDA_CHECK_LAUNCH();
+        RecordSink sink;
+        sink.gauss_rec = g.rec;
+        sink.records = reinterpret_cast<float4*>(b.records);
+        sink.ranges = im.ranges;
+        if (g_keep_sort_output) {      // inspection: also materialise the reference's sorted keys and point list
+            sink.keys64 = b.keys;
+            sink.point_list = (passes & 1) ? b.vals_alt : b.point_list;   // not the buffer the last pass reads
+        }
         prof_begin(ST_SORT, s);
-        launch_sort_pairs(k0, v0, k1, v1, R, passes, b.sort_scratch, s);
+        launch_sort_pairs(b.tkey, b.point_list, b.tkey_alt, b.vals_alt, R, passes, b.sort_scratch, s, &sink);
         SPLAT_STAGE_END(ST_SORT, s, passes + 2);
         SPLAT_CUDA_CHECK_LAUNCH();
     }
     (void)colors_precomp;   // colours were folded into the per-Gaussian record by the preprocess kernel
-    prof_begin(ST_RECORDS, s);
-    launch_ranges_and_records(R, gx * gy, g, b, im.ranges, s);
-    SPLAT_STAGE_END(ST_RECORDS, s, R > 0 ? 1 : 0);
     lane_end(caller, s);
     s = caller;
     SPLAT_CUDA_CHECK_LAUNCH();
     prof_begin(ST_RENDER_FWD, s);
     launch_render_forward(W, H, gx, gy, im.ranges, b.records, background, im.final_T, im.n_contrib, out_color,
-                          out_depth, out_opacity, n_touched, s);
+                          out_depth, out_opacity, n_touched, R > 0 ? sort_error_flag(b.sort_scratch) : nullptr, s);
     SPLAT_STAGE_END(ST_RENDER_FWD, s, 1);
     SPLAT_CUDA_CHECK_LAUNCH();
     return SPLAT_OK;
@@ -531,6 +533,12 @@ int splat_raster_allreduce_multimem(float* multicast, int world, int rank, size_
     return SPLAT_OK;
 }
 
+int splat_raster_keep_sort_output(int enable) {
+    const int was = g_keep_sort_output;
+    if (enable >= 0) g_keep_sort_output = enable ? 1 : 0;
+    return was;
+}
+
 int splat_raster_debug_views(int P, int R, int W, int H, void* geom, void* binning, void* image,
                              splat_raster_views* out) {
     if (!out || P < 0 || R < 0 || W <= 0 || H <= 0) return SPLAT_ERR_ARG;
@@ -545,7 +553,7 @@ int splat_raster_debug_views(int P, int R, int W, int H, void* geom, void* binni
     out->cov3D = g.cov3D;
     out->tiles_touched = g.tiles_touched;
     out->keys = reinterpret_cast<const unsigned long long*>(b.keys);
-    out->point_list = b.point_list;
+    out->point_list = (tile_sort_passes(gx, gy) & 1) ? b.vals_alt : b.point_list;
     out->ranges = reinterpret_cast<const unsigned int*>(im.ranges);
     out->final_T = im.final_T;
     out->n_contrib = im.n_contrib;

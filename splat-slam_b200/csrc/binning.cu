@@ -1,5 +1,5 @@
-// Binning: instance offsets, tile-key generation in depth order, tile ranges and the per-instance render records.
-// Together with radix_sort.cu this replaces cub::DeviceScan::InclusiveSum (DGR/cuda_rasterizer/rasterizer_impl.cu:280),
+// Binning: instance offsets and tile-key generation in depth order (tile ranges and the per-instance render records
+// come out of the last sort pass). Together with radix_sort.cu this replaces cub::DeviceScan::InclusiveSum (DGR/cuda_rasterizer/rasterizer_impl.cu:280),
 // duplicateWithKeys (:70-111), cub::DeviceRadixSort::SortPairs (:303-311), cudaMemset + identifyTileRanges
 // (:313-321,116-138).
 #include <cstdio>
@@ -83,7 +83,12 @@ void launch_depth_sort_and_offsets(int P, const GeomState& g, cudaStream_t s) {
 // Emission order per Gaussian is row-major over its tile rectangle, as in the reference.
 __global__ void __launch_bounds__(kPreBlock)
 duplicate_with_keys_kernel(int P, int grid_x, int grid_y, const int* __restrict__ radii, GeomState g,
-                           uint32_t* __restrict__ tkeys_out, uint32_t* __restrict__ vals_out) {
+                           uint32_t* __restrict__ tkeys_out, uint32_t* __restrict__ vals_out,
+                           uint2* __restrict__ ranges, int tiles) {
+    // preset of the tile ranges for the last sort pass (see radix_onesweep_kernel<true>): done here, by the first
+    // blocks, instead of by a memset node of its own
+    for (int t = blockIdx.x * kPreBlock + threadIdx.x; t < tiles; t += gridDim.x * kPreBlock)
+        ranges[t] = make_uint2(0xFFFFFFFFu, 0xFFFFFFFFu);
     // a depth sort whose look-back gave up must not go unnoticed: fail the stream loudly
     if (blockIdx.x == 0 && threadIdx.x == 0 && *sort_error_flag(g.sort_scratch) != 0u) {
         printf("splat_raster: depth sort look-back timed out\n");
@@ -145,64 +150,17 @@ duplicate_with_keys_kernel(int P, int grid_x, int grid_y, const int* __restrict_
 }
 
 void launch_duplicate_with_keys(int P, int grid_x, int grid_y, const int* radii, const GeomState& g,
-                                uint32_t* tkeys_out, uint32_t* vals_out, cudaStream_t s) {
+                                uint32_t* tkeys_out, uint32_t* vals_out, uint2* ranges, cudaStream_t s) {
     const int nblk = (P + kPreBlock - 1) / kPreBlock;
-    duplicate_with_keys_kernel<<<nblk, kPreBlock, 0, s>>>(P, grid_x, grid_y, radii, g, tkeys_out, vals_out);
+    duplicate_with_keys_kernel<<<nblk, kPreBlock, 0, s>>>(P, grid_x, grid_y, radii, g, tkeys_out, vals_out, ranges,
+                                                          grid_x * grid_y);
 }
 
-// ---- tile ranges + render records --------------------------------------------------------------------
-// One thread per sorted instance: detects tile boundaries (identifyTileRanges), materialises the reference's 64-bit
-// key (tile << 32 | depth bits) for inspection, and copies the instance's 48-byte per-Gaussian record
-// {x, y, id, footprint box | conic.x, conic.y, conic.z, opacity | r, g, b, depth} (written by
-// preprocess_forward_kernel) into sorted order, so the render kernels stream contiguous records with bulk async
-// copies instead of four dependent gathers per instance.
-__global__ void __launch_bounds__(256)
-ranges_and_records_kernel(int R, const uint32_t* __restrict__ tkeys, const uint32_t* __restrict__ point_list,
-                          const float4* __restrict__ gauss_rec, uint2* __restrict__ ranges,
-                          uint64_t* __restrict__ keys64, float4* __restrict__ records,
-                          const uint32_t* __restrict__ sort_error) {
-    if (blockIdx.x == 0 && threadIdx.x == 0 && *sort_error != 0u) {
-        printf("splat_raster: tile sort look-back timed out\n");
-        __trap();
-    }
-    __shared__ float4 s_t[256 / 32][32 * 3];
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    if (i < R) {
-        const uint32_t tile = tkeys[i];
-        if (i == 0) {
-            ranges[tile].x = 0;
-        } else {
-            const uint32_t prev = tkeys[i - 1];
-            if (tile != prev) { ranges[prev].y = i; ranges[tile].x = i; }
-        }
-        if (i == R - 1) ranges[tile].y = R;
-        // gather the Gaussian's 48-byte record (three 16-byte loads from one contiguous chunk)
-        const float4* src = gauss_rec + 3 * (size_t)point_list[i];
-        const float4 r2 = src[2];
-        s_t[warp][lane * 3 + 0] = src[0];
-        s_t[warp][lane * 3 + 1] = src[1];
-        s_t[warp][lane * 3 + 2] = r2;
-        keys64[i] = ((uint64_t)tile << 32) | (uint64_t)__float_as_uint(r2.w);
-    }
-    __syncwarp();
-    // the warp's 32 records are contiguous in the output: write them as three fully coalesced 512-byte rows
-    const int wbase = blockIdx.x * blockDim.x + warp * 32;
-    const int n = min(32, R - wbase) * 3;
-#pragma unroll
-    for (int k = 0; k < 3; ++k) {
-        const int e = k * 32 + lane;
-        if (e < n) records[3 * (size_t)wbase + e] = s_t[warp][e];
-    }
-}
-
-void launch_ranges_and_records(int R, int tiles, const GeomState& g, const BinningState& b, uint2* ranges,
-                               cudaStream_t s) {
-    cudaMemsetAsync(ranges, 0, sizeof(uint2) * (size_t)tiles, s);
-    if (R <= 0) return;
-    ranges_and_records_kernel<<<(R + 255) / 256, 256, 0, s>>>(R, b.tkey, b.point_list, g.rec, ranges, b.keys,
-                                                              reinterpret_cast<float4*>(b.records),
-                                                              sort_error_flag(b.sort_scratch));
+// ---- tile ranges ---------------------------------------------------------------------------------------
+// Tile ranges and the per-instance render records are produced by the last pass of the instance sort
+// (radix_sort.cu: radix_onesweep_kernel<true>); here only the preset every range starts from.
+void launch_reset_ranges(int tiles, uint2* ranges, cudaStream_t s) {
+    cudaMemsetAsync(ranges, 0xFF, sizeof(uint2) * (size_t)tiles, s);
 }
 
 }  // namespace splat

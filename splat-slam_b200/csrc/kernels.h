@@ -34,13 +34,20 @@ void launch_preprocess_backward(const BwdParams& p, const GeomState& g, cudaStre
 // binning.cu
 void launch_depth_sort_and_offsets(int P, const GeomState& g, cudaStream_t s);
 void launch_duplicate_with_keys(int P, int grid_x, int grid_y, const int* radii, const GeomState& g,
-                                uint32_t* tkeys_out, uint32_t* vals_out, cudaStream_t s);
-void launch_ranges_and_records(int R, int tiles, const GeomState& g, const BinningState& b, uint2* ranges,
-                               cudaStream_t s);
+                                uint32_t* tkeys_out, uint32_t* vals_out, uint2* ranges, cudaStream_t s);
+void launch_reset_ranges(int tiles, uint2* ranges, cudaStream_t s);
 // radix_sort.cu
 int tile_sort_passes(int grid_x, int grid_y);
+// where the last pass of the instance sort puts its result (see radix_onesweep_kernel<true>)
+struct RecordSink {
+    const float4* gauss_rec = nullptr;   // [3P] per-Gaussian render records
+    float4* records = nullptr;           // [3R] per-instance records in sorted order
+    uint2* ranges = nullptr;             // [tiles] preset to 0xFFFFFFFF (launch_reset_ranges)
+    uint64_t* keys64 = nullptr;          // [R] optional: the reference's sorted 64-bit keys, for inspection
+    uint32_t* point_list = nullptr;      // [R] optional: sorted Gaussian ids, for inspection
+};
 void launch_sort_pairs(uint32_t* k0, uint32_t* v0, uint32_t* k1, uint32_t* v1, int n, int passes, uint32_t* scratch,
-                       cudaStream_t s);
+                       cudaStream_t s, const RecordSink* sink = nullptr);
 // mapping_loss.cu
 int mapping_loss_blocks(int N);
 void launch_mapping_loss(int N, const float* image, const float* depth, const float* gt_image, const float* gt_depth,
@@ -84,9 +91,9 @@ constexpr int kMaxPeerRanks = 8;          // GPUs of one NVSwitch node
 int launch_allreduce_peer(float* const* buffers, int world, int rank, size_t count, cudaStream_t s);      // -> launches, < 0 unsupported
 int launch_allreduce_multimem(float* multicast, int world, int rank, size_t count, cudaStream_t s);       // -> launches
 // render.cu
-void launch_render_forward(int W, int H, int grid_x, int grid_y, const uint2* ranges, const float* records,
+void launch_render_forward(int W, int H, int grid_x, int grid_y, uint2* ranges, const float* records,
                            const float* bg, float* final_T, uint32_t* n_contrib, float* out_color, float* out_depth,
-                           float* out_opacity, int* n_touched, cudaStream_t s);
+                           float* out_opacity, int* n_touched, const uint32_t* sort_error, cudaStream_t s);
 void launch_render_backward(int W, int H, int grid_x, int grid_y, const uint2* ranges, const float* records,
                             const float* bg, const float* final_T, const uint32_t* n_contrib, const float* dL_dpix,
                             const float* dL_dpix_depth, float* grad_accum, cudaStream_t s);

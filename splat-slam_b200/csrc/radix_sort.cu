@@ -89,12 +89,24 @@ __global__ void __launch_bounds__(kRadix) radix_global_scan_kernel(uint32_t* __r
 }
 
 // ---- one pass ---------------------------------------------------------------------------------------------
+// kEmitRecords: the LAST pass of the instance sort. Its scatter already knows every instance's final position, so
+// instead of writing the sorted (tile, Gaussian id) pairs and having another kernel read them back, it gathers each
+// Gaussian's 48-byte render record straight into sorted order (what ranges_and_records_kernel did in round 1) and
+// marks the tile ranges: equal tiles are adjacent inside a sort tile, the first and last instance of every such run
+// lower ranges[tile].x to their position / ranges[tile].y to ~(position + 1) with atomicMin (both start at
+// 0xFFFFFFFF; render_forward_kernel rewrites its tile's entry as [start, end), or (0, 0) for an empty tile, which is
+// identifyTileRanges' result, DGR/cuda_rasterizer/rasterizer_impl.cu:116-138).
+template <bool kEmitRecords>
 __global__ void __launch_bounds__(kSortThreads, 3)
 radix_onesweep_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
                       uint32_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out, int n, int shift,
                       const uint32_t* __restrict__ gbase, uint32_t* tile_state, uint32_t* ticket,
-                      uint32_t* error_flag, int ntiles) {
-    __shared__ uint32_t s_cnt[kWarps][kRadix];       // per-warp digit counts -> per-warp local positions
+                      uint32_t* error_flag, int ntiles, RecordSink sink) {
+    // per-warp digit counts -> per-warp local positions; with kEmitRecords the same words later stage the records
+    // of 32 instances per warp (96 float4 = 384 words each)
+    constexpr int kCntWords = kEmitRecords ? kWarps * 384 : kWarps * kRadix;
+    __shared__ __align__(16) uint32_t s_cnt_raw[kCntWords];
+    uint32_t (*s_cnt)[kRadix] = reinterpret_cast<uint32_t (*)[kRadix]>(s_cnt_raw);
     __shared__ __align__(16) uint2 s_kv[kSortTile];  // reorder buffer (key, value)
     __shared__ uint32_t s_goff[kRadix];              // global offset of the digit run minus its local base
     __shared__ uint32_t s_scan[kWarps];
@@ -206,19 +218,59 @@ radix_onesweep_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __re
     }
     __syncthreads();
     const int n_valid = min(kSortTile, n - tile * kSortTile);
-    for (int i = threadIdx.x; i < n_valid; i += kSortThreads) {
-        const uint2 kv = s_kv[i];
-        const uint32_t pos = s_goff[(kv.x >> shift) & (kRadix - 1)] + i;
-        keys_out[pos] = kv.x;
-        vals_out[pos] = kv.y;
+    if constexpr (!kEmitRecords) {
+        for (int i = threadIdx.x; i < n_valid; i += kSortThreads) {
+            const uint2 kv = s_kv[i];
+            const uint32_t pos = s_goff[(kv.x >> shift) & (kRadix - 1)] + i;
+            keys_out[pos] = kv.x;
+            vals_out[pos] = kv.y;
+        }
+    } else {
+        // (Gathering four instances per thread at a time and storing straight from registers, without the transposition,
+        // was measured and is slower: 0.182 vs 0.173 ms for the pass.)
+        float4* s_t = reinterpret_cast<float4*>(s_cnt_raw) + warp * 96;   // the digit counts are dead by now
+        for (int base = 0; base < n_valid; base += kSortThreads) {
+            const int i = base + (int)threadIdx.x;
+            uint32_t pos = 0;
+            if (i < n_valid) {
+                const uint2 kv = s_kv[i];
+                pos = s_goff[(kv.x >> shift) & (kRadix - 1)] + (uint32_t)i;
+                // first / last instance of a run of equal tiles inside this sort tile (~0 is never a tile id)
+                const uint32_t prev = (i > 0) ? s_kv[i - 1].x : 0xFFFFFFFFu;
+                const uint32_t next = (i + 1 < n_valid) ? s_kv[i + 1].x : 0xFFFFFFFFu;
+                if (prev != kv.x) atomicMin(&sink.ranges[kv.x].x, pos);
+                if (next != kv.x) atomicMin(&sink.ranges[kv.x].y, ~(pos + 1u));
+                const float4* src = sink.gauss_rec + 3 * (size_t)kv.y;
+                const float4 r0 = __ldg(src), r1 = __ldg(src + 1), r2 = __ldg(src + 2);
+                s_t[lane * 3 + 0] = r0;
+                s_t[lane * 3 + 1] = r1;
+                s_t[lane * 3 + 2] = r2;
+                if (sink.keys64 != nullptr) {      // inspection only (splat_raster_keep_sort_output)
+                    sink.keys64[pos] = ((uint64_t)kv.x << 32) | (uint64_t)__float_as_uint(r2.w);
+                    sink.point_list[pos] = kv.y;
+                }
+            }
+            __syncwarp();
+            // 32 records = 96 float4, mostly contiguous in the output (a digit run is): lane l writes parts l, l+32, l+64
+            const int wbase = base + warp * 32;
+#pragma unroll
+            for (int k = 0; k < 3; ++k) {
+                const int e = k * 32 + lane;
+                const int el = e / 3, part = e - 3 * el;
+                const uint32_t p = __shfl_sync(0xffffffffu, pos, el);
+                if (wbase + el < n_valid) sink.records[3 * (size_t)p + part] = s_t[e];
+            }
+            __syncwarp();
+        }
     }
 }
 
 // Stable LSD sort of n (key, value) pairs on key bits [0, 8*passes). Ping-pongs between (k0, v0) and (k1, v1): the
 // input is read from (k0, v0); the result lands in (k0, v0) for an even pass count and in (k1, v1) for an odd one.
+// With `sink` the last pass emits render records and tile ranges instead of the sorted pairs (see the kernel).
 // scratch: SortScratch::words(n) zero-initialised-by-us 32-bit words.
 void launch_sort_pairs(uint32_t* k0, uint32_t* v0, uint32_t* k1, uint32_t* v1, int n, int passes, uint32_t* scratch,
-                       cudaStream_t s) {
+                       cudaStream_t s, const RecordSink* sink) {
     if (n <= 0 || passes <= 0) return;
     const int ntiles = (n + kSortTile - 1) / kSortTile;
     // scratch: [4][256] digit histograms, [4] tickets, error flag (64 words), then [passes][ntiles][256] tile states
@@ -232,9 +284,14 @@ void launch_sort_pairs(uint32_t* k0, uint32_t* v0, uint32_t* k1, uint32_t* v1, i
     radix_global_scan_kernel<<<passes, kRadix, 0, s>>>(ghist);
     uint32_t *kin = k0, *vin = v0, *kout = k1, *vout = v1;
     for (int p = 0; p < passes; ++p) {
-        radix_onesweep_kernel<<<ntiles, kSortThreads, 0, s>>>(kin, vin, kout, vout, n, p * kRadixBits,
-                                                             ghist + p * kRadix, states + (size_t)p * ntiles * kRadix,
-                                                             tickets + p, error_flag, ntiles);
+        if (sink != nullptr && p == passes - 1)
+            radix_onesweep_kernel<true><<<ntiles, kSortThreads, 0, s>>>(
+                kin, vin, kout, vout, n, p * kRadixBits, ghist + p * kRadix, states + (size_t)p * ntiles * kRadix,
+                tickets + p, error_flag, ntiles, *sink);
+        else
+            radix_onesweep_kernel<false><<<ntiles, kSortThreads, 0, s>>>(
+                kin, vin, kout, vout, n, p * kRadixBits, ghist + p * kRadix, states + (size_t)p * ntiles * kRadix,
+                tickets + p, error_flag, ntiles, RecordSink());
         uint32_t* tk = kin; kin = kout; kout = tk;
         uint32_t* tv = vin; vin = vout; vout = tv;
     }

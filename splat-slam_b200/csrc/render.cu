@@ -3,11 +3,12 @@
 //
 // B200 design: one CTA per 16x16 tile (tile ids/ranges stay bit-compatible with the reference). Each warp owns
 // an 8x4 pixel patch so whole-warp rejection of a Gaussian is likely. Per-instance 48-byte records (built in
-// sorted order by ranges_and_records_kernel) are streamed into a shared-memory ring with cp.async.bulk (TMA 1-D
+// sorted order by the last pass of the instance sort) are streamed into a shared-memory ring with cp.async.bulk (TMA 1-D
 // bulk copy, SASS UBLKCP) completing on an mbarrier; the consumer loops read them with broadcast LDS.128.
 // The backward takes the per-Gaussian sums in a transposed second phase (lane = Gaussian) instead of a cross-lane
 // reduction, and its warps walk the ring independently (no block barrier per batch); see render_backward_kernel.
 #include <cuda_fp16.h>
+#include <cstdio>
 #include <cstdlib>
 #include "common.cuh"
 #include "kernels.h"
@@ -60,7 +61,7 @@ __device__ __forceinline__ float4 patch_of_warp(int tile_x, int tile_y) {
 }
 
 // Per-warp binning of one staged batch: each lane tests cnt/32 records against the warp's pixel patch using the
-// conservative footprint box stored in the record (ranges_and_records_kernel) and the survivors' batch indices are
+// conservative footprint box stored in the record (preprocess_forward_kernel) and the survivors' batch indices are
 // compacted, in order, into `list`. A (warp, instance) pair that cannot reach alpha >= 1/255 anywhere in the patch
 // then costs ~0.5 instructions instead of a full power/exp evaluation by all 32 lanes. Comparisons are written so
 // that NaN coordinates count as "inside" (the reference would still evaluate them). Returns the survivor count.
@@ -91,16 +92,54 @@ __device__ __forceinline__ int bin_batch_for_warp(const float4* rec, int cnt, fl
 // =====================================================================================================
 // forward
 // =====================================================================================================
+// try_wait once; true when the phase with this parity has completed
+__device__ __forceinline__ bool mbar_try(uint64_t* bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+    return ok != 0;
+}
+
+constexpr int kFwdRecs = 64;     // records per ring stage
+constexpr int kFwdStages = 8;    // stages of the record ring
+
+// volatile read of a shared-memory word by its 32-bit shared address (a C++ volatile cast would go through a generic
+// pointer and make ptxas address every shared array of the kernel through the generic window)
+__device__ __forceinline__ int lds_volatile(uint32_t addr) {
+    int v;
+    asm volatile("ld.volatile.shared.s32 %0, [%1];" : "=r"(v) : "r"(addr) : "memory");
+    return v;
+}
+
+// The warps of a tile see very different numbers of Gaussians (per-warp binning) and saturate at different depths, so
+// they do not meet at block barriers: every warp walks the ring of record batches at its own pace, waiting only for
+// "stage full" (mbarrier completed by the bulk copy). When a warp is done with a stage its lane 0 counts itself off
+// and the LAST warp to do so re-arms the stage with the batch kFwdStages further on. A warp whose 32 pixels are all
+// saturated (or outside the image) keeps counting itself off without looking at the records; when all eight are in
+// that state nobody refills and everybody leaves (the reference's "whole tile done" exit, forward.cu:318-320).
 __global__ void __launch_bounds__(SPLAT_TILE_PIXELS)
-render_forward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ranges, const float* __restrict__ records,
+render_forward_kernel(int W, int H, int grid_x, uint2* __restrict__ ranges, const float* __restrict__ records,
                       const float* __restrict__ bg, float* __restrict__ final_T, uint32_t* __restrict__ n_contrib,
                       float* __restrict__ out_color, float* __restrict__ out_depth, float* __restrict__ out_opacity,
-                      int* __restrict__ n_touched) {
-    __shared__ __align__(128) float4 s_rec[2][kBatch * 3];
-    __shared__ __align__(8) uint64_t s_bar[2];
-    __shared__ int s_cnt[2][kBatch];
-    __shared__ uint8_t s_list[SPLAT_TILE_PIXELS / 32][kBatch];
-    __shared__ uint32_t s_tv[SPLAT_TILE_PIXELS / 32][kBatch];
+                      int* __restrict__ n_touched, const uint32_t* __restrict__ sort_error) {
+    // an instance sort whose look-back gave up must not go unnoticed: fail the stream loudly
+    if (blockIdx.x == 0 && threadIdx.x == 0 && sort_error != nullptr && *sort_error != 0u) {
+        printf("splat_raster: tile sort look-back timed out\n");
+        __trap();
+    }
+    constexpr int kWarps = SPLAT_TILE_PIXELS / 32;
+    __shared__ __align__(128) float4 s_rec[kFwdStages][kFwdRecs * 3];
+    __shared__ __align__(8) uint64_t s_full[kFwdStages];
+    __shared__ int s_done[kFwdStages];          // warps that are through with the stage's current batch
+    __shared__ int s_saturated;                 // warps with nothing left to blend
+    __shared__ int s_issued;                    // batches handed to the copy engine so far
+    __shared__ uint8_t s_list[kWarps][kFwdRecs];
+    __shared__ uint32_t s_tv[kWarps][kFwdRecs];
 
     const int tile = blockIdx.x;
     const int tile_x = tile % grid_x, tile_y = tile / grid_x;
@@ -111,90 +150,145 @@ render_forward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ranges
     const float pixfx = (float)px, pixfy = (float)py;
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const float4 patch = patch_of_warp(tile_x, tile_y);
+    uint8_t* my_list = s_list[warp];
+    uint32_t* my_tv = s_tv[warp];
+    const uint32_t saturated_a = smem_u32(&s_saturated), issued_a = smem_u32(&s_issued);
+    uint32_t tv_a = smem_u32(my_tv);
+    asm volatile("mov.u32 %0, %0;" : "+r"(tv_a));     // opaque: keeps ptxas from re-deriving the address in the hot loop
 
-    const uint2 range = ranges[tile];
+    // The sort leaves (first position, ~(last position + 1)) per tile, both 0xFFFFFFFF for a tile without instances;
+    // this CTA is the tile's first reader and rewrites the entry as [start, end) / (0, 0) for everybody after it
+    // (the backward, inspection): the reference's identifyTileRanges result.
+    uint2 range = ranges[tile];
+    range.y = ~range.y;
+    if (range.y <= range.x) range = make_uint2(0u, 0u);
     const int n = (int)(range.y - range.x);
-    const int nb = (n + kBatch - 1) / kBatch;
+    const int nb = (n + kFwdRecs - 1) / kFwdRecs;
     const float4* src = reinterpret_cast<const float4*>(records) + 3 * (size_t)range.x;
+    auto fill = [&](int b) {   // one thread: bulk copy of batch b into its ring stage
+        const int cnt = min(kFwdRecs, n - b * kFwdRecs);
+        bulk_load(&s_rec[b % kFwdStages][0], src + 3 * (size_t)b * kFwdRecs, (uint32_t)cnt * 48u, &s_full[b % kFwdStages]);
+    };
 
-    if (threadIdx.x == 0) { mbar_init(&s_bar[0], 1); mbar_init(&s_bar[1], 1); fence_mbar_init(); }
-    if (threadIdx.x < kBatch) { s_cnt[0][threadIdx.x] = 0; s_cnt[1][threadIdx.x] = 0; }
-    __syncthreads();
     if (threadIdx.x == 0) {
-        for (int b = 0; b < 2 && b < nb; ++b) {
-            const int cnt = min(kBatch, n - b * kBatch);
-            bulk_load(&s_rec[b][0], src + 3 * (size_t)b * kBatch, (uint32_t)cnt * 48u, &s_bar[b]);
-        }
+        for (int st = 0; st < kFwdStages; ++st) { mbar_init(&s_full[st], 1); s_done[st] = 0; }
+        s_saturated = 0;
+        s_issued = min(kFwdStages, nb);
+        fence_mbar_init();
+    }
+    __syncthreads();                       // barriers armed; every thread has read the raw range entry
+    if (threadIdx.x == 0) {
+        ranges[tile] = range;
+        for (int b = 0; b < kFwdStages && b < nb; ++b) fill(b);
     }
 
     bool done = !inside;
     float T = 1.0f, C0 = 0.0f, C1 = 0.0f, C2 = 0.0f, Dp = 0.0f;
     uint32_t last_contributor = 0;
+    bool warp_done = __all_sync(0xffffffffu, done);
+    if (warp_done && lane == 0) atomicAdd(&s_saturated, 1);
 
     int b = 0;
     for (; b < nb; ++b) {
-        // whole tile saturated -> stop (forward.cu:318-320)
-        if (__syncthreads_count(done) == SPLAT_TILE_PIXELS) break;
-        const int stage = b & 1;
-        const int cnt = min(kBatch, n - b * kBatch);
-        mbar_wait(&s_bar[stage], (uint32_t)((b >> 1) & 1));
-        const float4* rec = &s_rec[stage][0];
-        const int n_live = __all_sync(0xffffffffu, done) ? 0 : bin_batch_for_warp(rec, cnt, patch, s_list[warp], lane);
-        int k = 0;
-        for (; k < n_live; ++k) {
-            // survivors of the binning almost always touch some lane, so everything up to the blend is evaluated
-            // unconditionally and a single ballot per instance serves both the blend and the n_touched count
-            const int j = s_list[warp][k];
-            const float4 r0 = rec[3 * j];          // x, y, id, footprint box
-            const float4 r1 = rec[3 * j + 1];      // conic.x, conic.y, conic.z, opacity
-            const float dx = fsub(r0.x, pixfx), dy = fsub(r0.y, pixfy);
-            const float power = gauss_power_ref(dx, dy, r1.x, r1.y, r1.z);
-            // alpha = min(0.99, opacity * exp(power)); 1/255 cut; transmittance test (forward.cu:350-363)
-            const float alpha = fminf(0.99f, fmul(r1.w, expf(power)));
-            const float test_T = fmul(T, fsub(1.0f, alpha));
-            bool act = !done && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
-            if (act && test_T < 0.0001f) { done = true; act = false; }
-            if (act) {
-                const float4 r2 = rec[3 * j + 2];  // r, g, b, depth
-                // C += c * alpha * T as fma(T, alpha*c, C) (reference SASS order)
-                C0 = ffma(T, fmul(alpha, r2.x), C0);
-                C1 = ffma(T, fmul(alpha, r2.y), C1);
-                C2 = ffma(T, fmul(alpha, r2.z), C2);
-                Dp = ffma(T, fmul(alpha, r2.w), Dp);
-                T = test_T;
-                last_contributor = (uint32_t)(b * kBatch + j + 1);
+        const int stage = b % kFwdStages;
+        // wait for the batch - unless the whole tile has saturated in the meantime and nobody refills any more
+        bool stop = false;
+        for (;;) {
+            const bool ok = mbar_try(&s_full[stage], (uint32_t)((b / kFwdStages) & 1));
+            if (__all_sync(0xffffffffu, ok)) break;
+            if (__any_sync(0xffffffffu, lds_volatile(saturated_a) == kWarps)) { stop = true; break; }
+        }
+        if (stop) break;
+        if (!warp_done) {
+            const int cnt = min(kFwdRecs, n - b * kFwdRecs);
+            const float4* rec = &s_rec[stage][0];
+            const int n_live = bin_batch_for_warp<kFwdRecs>(rec, cnt, patch, my_list, lane);
+            // n_touched counts pixels that blend a Gaussian while still > 50 % transparent (forward.cu:368-370). T only
+            // falls, so once none of the warp's pixels is above 0.5 the vote, its store and the counting below are dead
+            // weight for the rest of the tile (most of a deep tile): that case runs a loop without them.
+            const bool counting = __any_sync(0xffffffffu, !done && T > 0.5f);
+            int k = 0;
+            if (counting) {
+                for (; k < n_live; ++k) {
+                    // survivors of the binning almost always touch some lane, so everything up to the blend is evaluated
+                    // unconditionally and a single ballot per instance serves the n_touched count
+                    const int j = my_list[k];
+                    const float4 r0 = rec[3 * j];          // x, y, id, footprint box
+                    const float4 r1 = rec[3 * j + 1];      // conic.x, conic.y, conic.z, opacity
+                    const float dx = fsub(r0.x, pixfx), dy = fsub(r0.y, pixfy);
+                    const float power = gauss_power_ref(dx, dy, r1.x, r1.y, r1.z);
+                    // alpha = min(0.99, opacity * exp(power)); 1/255 cut; transmittance test (forward.cu:350-363)
+                    const float alpha = fminf(0.99f, fmul(r1.w, expf(power)));
+                    const float test_T = fmul(T, fsub(1.0f, alpha));
+                    bool act = !done && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
+                    if (act && test_T < 0.0001f) { done = true; act = false; }
+                    if (act) {
+                        const float4 r2 = rec[3 * j + 2];  // r, g, b, depth
+                        // C += c * alpha * T as fma(T, alpha*c, C) (reference SASS order)
+                        C0 = ffma(T, fmul(alpha, r2.x), C0);
+                        C1 = ffma(T, fmul(alpha, r2.y), C1);
+                        C2 = ffma(T, fmul(alpha, r2.z), C2);
+                        Dp = ffma(T, fmul(alpha, r2.w), Dp);
+                        T = test_T;
+                        last_contributor = (uint32_t)(b * kFwdRecs + j + 1);
+                    }
+                    // the vote is only parked here; it is counted for 32 instances at a time below
+                    const uint32_t tv = __ballot_sync(0xffffffffu, act && test_T > 0.5f);
+                    asm volatile("{\n\t.reg .pred p;\n\tsetp.eq.u32 p, %0, 0;\n\t@p st.shared.u32 [%1], %2;\n\t}"
+                                 ::"r"(lane), "r"(tv_a + 4u * (uint32_t)k), "r"(tv) : "memory");
+                    if (__all_sync(0xffffffffu, done)) { ++k; break; }
+                }
+                __syncwarp();
+                // one atomic per (warp, Gaussian) with votes instead of one per pixel
+                for (int i = (int)lane; i < k; i += 32) {
+                    const int c = __popc(my_tv[i]);
+                    if (c) atomicAdd(&n_touched[__float_as_int(rec[3 * my_list[i]].z)], c);
+                }
+            } else {
+                for (; k < n_live; ++k) {
+                    const int j = my_list[k];
+                    const float4 r0 = rec[3 * j];
+                    const float4 r1 = rec[3 * j + 1];
+                    const float dx = fsub(r0.x, pixfx), dy = fsub(r0.y, pixfy);
+                    const float power = gauss_power_ref(dx, dy, r1.x, r1.y, r1.z);
+                    const float alpha = fminf(0.99f, fmul(r1.w, expf(power)));
+                    const float test_T = fmul(T, fsub(1.0f, alpha));
+                    bool act = !done && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
+                    if (act && test_T < 0.0001f) { done = true; act = false; }
+                    if (__any_sync(0xffffffffu, act)) {
+                        const float4 r2 = rec[3 * j + 2];
+                        // same arithmetic, predicated per lane instead of branched
+                        const float c0 = ffma(T, fmul(alpha, r2.x), C0), c1 = ffma(T, fmul(alpha, r2.y), C1);
+                        const float c2 = ffma(T, fmul(alpha, r2.z), C2), dp = ffma(T, fmul(alpha, r2.w), Dp);
+                        C0 = act ? c0 : C0;
+                        C1 = act ? c1 : C1;
+                        C2 = act ? c2 : C2;
+                        Dp = act ? dp : Dp;
+                        T = act ? test_T : T;
+                        last_contributor = act ? (uint32_t)(b * kFwdRecs + j + 1) : last_contributor;
+                    } else if (__all_sync(0xffffffffu, done)) {
+                        break;
+                    }
+                }
             }
-            // n_touched: pixels that blended this Gaussian while still > 50 % transparent (forward.cu:368-370). The vote
-            // is only parked here; counting and the shared-memory add are done for 32 instances at a time below.
-            const uint32_t tv = __ballot_sync(0xffffffffu, act && test_T > 0.5f);
-            if (lane == 0) s_tv[warp][k] = tv;
-            if (__all_sync(0xffffffffu, done)) { ++k; break; }
-        }
-        __syncwarp();
-        for (int i = (int)lane; i < k; i += 32) {
-            const int c = __popc(s_tv[warp][i]);
-            if (c) atomicAdd(&s_cnt[stage][s_list[warp][i]], c);
-        }
-        __syncthreads();   // every warp is done with this stage
-        if (threadIdx.x < cnt) {
-            const int c = s_cnt[stage][threadIdx.x];
-            if (c) {
-                atomicAdd(&n_touched[__float_as_int(rec[3 * threadIdx.x].z)], c);
-                s_cnt[stage][threadIdx.x] = 0;
+            if (__all_sync(0xffffffffu, done)) {
+                warp_done = true;
+                if (lane == 0) atomicAdd(&s_saturated, 1);
             }
         }
-        __syncthreads();   // ids read before the stage is overwritten
-        if (threadIdx.x == 0 && b + 2 < nb) {
-            const int cnt2 = min(kBatch, n - (b + 2) * kBatch);
-            fence_proxy_async();
-            bulk_load(&s_rec[stage][0], src + 3 * (size_t)(b + 2) * kBatch, (uint32_t)cnt2 * 48u, &s_bar[stage]);
+        __syncwarp();                                  // every lane has read what it needs from this stage
+        if (lane == 0) {
+            __threadfence_block();
+            if (atomicAdd(&s_done[stage], 1) == kWarps - 1) {
+                s_done[stage] = 0;                     // published to the other warps by the refill's mbarrier
+                if (b + kFwdStages < nb && lds_volatile(saturated_a) < kWarps) {
+                    __threadfence_block();
+                    fence_proxy_async();
+                    fill(b + kFwdStages);
+                    atomicMax(&s_issued, b + kFwdStages + 1);
+                }
+            }
         }
-    }
-
-    // an early stop leaves up to two bulk copies in flight: they must land before this CTA's shared memory
-    // can be handed to another CTA
-    if (threadIdx.x == 0) {
-        for (int k = b; k < nb && k < b + 2; ++k) mbar_wait(&s_bar[k & 1], (uint32_t)((k >> 1) & 1));
     }
 
     if (inside) {
@@ -207,14 +301,22 @@ render_forward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ranges
         out_depth[pix_id] = Dp;
         out_opacity[pix_id] = fsub(1.0f, T);
     }
+
+    // an early stop leaves bulk copies in flight that nobody waited for: they must land before this CTA's shared
+    // memory can be handed to another CTA
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const int issued = lds_volatile(issued_a);
+        for (int k = b; k < issued; ++k) mbar_wait(&s_full[k % kFwdStages], (uint32_t)((k / kFwdStages) & 1));
+    }
 }
 
-void launch_render_forward(int W, int H, int grid_x, int grid_y, const uint2* ranges, const float* records,
+void launch_render_forward(int W, int H, int grid_x, int grid_y, uint2* ranges, const float* records,
                            const float* bg, float* final_T, uint32_t* n_contrib, float* out_color, float* out_depth,
-                           float* out_opacity, int* n_touched, cudaStream_t s) {
+                           float* out_opacity, int* n_touched, const uint32_t* sort_error, cudaStream_t s) {
     render_forward_kernel<<<grid_x * grid_y, SPLAT_TILE_PIXELS, 0, s>>>(W, H, grid_x, ranges, records, bg, final_T,
                                                                         n_contrib, out_color, out_depth, out_opacity,
-                                                                        n_touched);
+                                                                        n_touched, sort_error);
 }
 
 // =====================================================================================================

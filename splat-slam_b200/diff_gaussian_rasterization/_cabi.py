@@ -39,6 +39,7 @@ EXPORTS = (
     "splat_raster_deform_points", "splat_raster_activations_forward", "splat_raster_activations_backward", "splat_raster_priority_lanes",
     "splat_raster_backward_noalloc", "splat_raster_set_debug", "splat_raster_last_failed_stage",
     "splat_raster_debug_sync_count", "splat_raster_allreduce_peer", "splat_raster_allreduce_multimem",
+    "splat_raster_keep_sort_output",
 )
 
 
@@ -128,8 +129,17 @@ def stream_ptr(device) -> int:
     return torch.cuda.current_stream(device).cuda_stream
 
 
+def keep_sort_output(enable: bool | None = None) -> bool:
+    """Make forwards materialise the sorted 64-bit keys and the point list for `debug_views` (tests only)."""
+    L = lib()
+    L.splat_raster_keep_sort_output.restype = c_int
+    L.splat_raster_keep_sort_output.argtypes = [c_int]
+    return bool(L.splat_raster_keep_sort_output(-1 if enable is None else int(bool(enable))))
+
+
 def debug_views(P, R, W, H, geom, binning, image):
-    """Tensor copies of the private intermediate arrays (tests only)."""
+    """Tensor copies of the private intermediate arrays (tests only; keys / point_list need `keep_sort_output(True)`
+    during the forward)."""
     v = _Views()
     check(lib().splat_raster_debug_views(P, R, W, H, geom.data_ptr(), binning.data_ptr(), image.data_ptr(),
                                          ctypes.byref(v)), "debug_views")

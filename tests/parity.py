@@ -238,10 +238,14 @@ def ours_forward_with_intermediates(case, device="cuda"):
     def opt(t):
         return e if t is None else t.to(device)
 
-    R, color, radii, geom, binning, img, depth, opacity, n_touched = m._forward_impl(
-        S, case["means3D"].to(device), opt(case["shs"]), opt(case["colors_precomp"]), case["opacities"].to(device),
-        opt(case["scales"]), opt(case["rotations"]), opt(case["cov3D_precomp"]))
-    torch.cuda.synchronize()
+    was = _cabi.keep_sort_output(True)     # the product path does not write the sorted keys / point list
+    try:
+        R, color, radii, geom, binning, img, depth, opacity, n_touched = m._forward_impl(
+            S, case["means3D"].to(device), opt(case["shs"]), opt(case["colors_precomp"]), case["opacities"].to(device),
+            opt(case["scales"]), opt(case["rotations"]), opt(case["cov3D_precomp"]))
+        torch.cuda.synchronize()
+    finally:
+        _cabi.keep_sort_output(was)
     P = case["means3D"].shape[0]
     out = _cabi.debug_views(P, R, S.image_width, S.image_height, geom, binning, img)
     out.update(num_rendered=R, color=color, radii=radii, depth=depth, opacity=opacity, n_touched=n_touched)

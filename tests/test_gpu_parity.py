@@ -293,15 +293,15 @@ def test_debug_mode_checks_every_stage_and_names_the_failing_one(tmp_path, monke
     monkeypatch.setattr(T, "settings_for", lambda mod, c, device="cuda": S)
     _cabi.debug_sync_count(reset=True)
     dbg = T.run_module(m, case_dbg)
-    # forward: preprocess, depth sort, key emission, tile sort, records, render; backward: clear, render, per-Gaussian
-    assert _cabi.debug_sync_count(reset=True) == 9
+    # forward: preprocess, depth sort, key emission, tile sort (+ records, ranges), render; backward: clear, render, per-Gaussian
+    assert _cabi.debug_sync_count(reset=True) == 8
     assert not _cabi.set_debug(False), "debug mode must be switched off again after the call"
     for k in ("color", "depth", "radii", "n_touched"):
         assert torch.equal(plain[k], dbg[k]), k
     assert T.rel_err(dbg["grad_means3D"], plain["grad_means3D"]) <= T.GRAD_RTOL
     assert not os.path.exists("snapshot_fw.dump") and not os.path.exists("snapshot_bw.dump")
     # a failing forward stage: named in the exception, inputs dumped
-    monkeypatch.setattr(m, "_debug_fail_stage", _cabi.stage_index("tile_sort"))
+    monkeypatch.setattr(m, "_debug_fail_stage", _cabi.stage_index("tile_sort_records_ranges"))
     with pytest.raises(_cabi.SplatRasterError, match="tile_sort"):
         T.run_module(m, case_dbg)
     dump = torch.load("snapshot_fw.dump", weights_only=False)
