@@ -150,6 +150,34 @@ int splat_raster_mark_visible(int P, const float* means3D, const float* viewmatr
  * out: 5 floats = (loss, sum l1_rgb, sum l1_depth, dL/da, dL/db), summed in a fixed order (run-to-run deterministic).
  * Gradients are for dL/dloss = 1. */
 int splat_raster_mapping_loss_blocks(int W, int H);
+
+/* The same loss evaluated in the epilogue of the forward renderer, from the pixel's colour and depth still in
+ * registers: splat_raster_forward_render_loss = splat_raster_forward_render + this descriptor. dL/dimage and dL/ddepth
+ * are written next to the images, `out` as for splat_raster_mapping_loss (the sums run over tiles instead of blocks
+ * of 256 pixels, so `out` agrees with the stand-alone kernel to rounding, not bit for bit; the gradients are
+ * identical). One launch and one pass over the images less per view (slam_utils.py:71-105 follows every render of a
+ * mapping step, reference src/mapper.py:426-490). workspace: 4 + 4 * splat_raster_loss_partials(W, H) floats, ticket
+ * word zero on entry as above. */
+typedef struct splat_raster_loss_desc {
+    const float* gt_image;      /* [3*H*W] */
+    const float* gt_depth;      /* [H*W] */
+    const float* exposure_a;    /* one device float; NULL with initialization */
+    const float* exposure_b;
+    float alpha;
+    float rgb_boundary_threshold;
+    int initialization;
+    float* workspace;
+    float* out;                 /* [5] */
+    float* dL_dimage;           /* [3*H*W] */
+    float* dL_ddepth;           /* [H*W] */
+} splat_raster_loss_desc;
+int splat_raster_loss_partials(int W, int H);
+int splat_raster_forward_render_loss(
+    int P, int R, int W, int H, const float* background, const float* colors_precomp, const int* radii,
+    void* geom, void* binning, void* image,
+    float* out_color, float* out_depth, float* out_opacity, int* n_touched,
+    const splat_raster_loss_desc* loss, void* stream);
+
 int splat_raster_mapping_loss(int W, int H, const float* image, const float* depth, const float* gt_image,
                               const float* gt_depth, const float* exposure_a, const float* exposure_b, float alpha,
                               float rgb_boundary_threshold, int initialization, float* workspace, float* out,

@@ -262,9 +262,26 @@ int splat_raster_forward_wait(void) {
     return e == cudaSuccess ? SPLAT_OK : (int)e;
 }
 
-int splat_raster_forward_render(int P, int R, int W, int H, const float* background, const float* colors_precomp,
-                                const int* radii, void* geom, void* binning, void* image, float* out_color,
-                                float* out_depth, float* out_opacity, int* n_touched, void* stream) {
+}  // extern "C"
+
+namespace {
+int loss_desc_from_abi(int W, int H, const splat_raster_loss_desc* in, LossDesc* out) {
+    if (W <= 0 || H <= 0) return SPLAT_ERR_SIZE;
+    if (!in->gt_image || !in->gt_depth || !in->workspace || !in->out || !in->dL_dimage || !in->dL_ddepth)
+        return SPLAT_ERR_ARG;
+    if ((reinterpret_cast<uintptr_t>(in->workspace) & 15u) != 0) return SPLAT_ERR_ARG;
+    if (!in->initialization && (!in->exposure_a || !in->exposure_b)) return SPLAT_ERR_ARG;
+    out->gt_image = in->gt_image; out->gt_depth = in->gt_depth;
+    out->exposure_a = in->exposure_a; out->exposure_b = in->exposure_b;
+    out->alpha = in->alpha; out->rgb_boundary_threshold = in->rgb_boundary_threshold;
+    out->initialization = in->initialization;
+    out->workspace = in->workspace; out->out = in->out; out->dL_dimage = in->dL_dimage; out->dL_ddepth = in->dL_ddepth;
+    return SPLAT_OK;
+}
+
+int forward_render_impl(int P, int R, int W, int H, const float* background, const float* colors_precomp,
+                        const int* radii, void* geom, void* binning, void* image, float* out_color,
+                        float* out_depth, float* out_opacity, int* n_touched, const LossDesc* loss, void* stream) {
     if (P < 0 || R < 0 || W <= 0 || H <= 0) return SPLAT_ERR_SIZE;
     if (!geom || !binning || !image || !background || !out_color || !out_depth || !out_opacity) return SPLAT_ERR_ARG;
     if (P > 0 && (!radii || !n_touched)) return SPLAT_ERR_ARG;
@@ -301,10 +318,38 @@ int splat_raster_forward_render(int P, int R, int W, int H, const float* backgro
     SPLAT_CUDA_CHECK_LAUNCH();
     prof_begin(ST_RENDER_FWD, s);
     launch_render_forward(W, H, gx, gy, im.ranges, b.records, background, im.final_T, im.n_contrib, out_color,
-                          out_depth, out_opacity, n_touched, R > 0 ? sort_error_flag(b.sort_scratch) : nullptr, s);
+                          out_depth, out_opacity, n_touched, R > 0 ? sort_error_flag(b.sort_scratch) : nullptr, loss, s);
     SPLAT_STAGE_END(ST_RENDER_FWD, s, 1);
     SPLAT_CUDA_CHECK_LAUNCH();
     return SPLAT_OK;
+}
+}  // namespace
+
+extern "C" {
+
+int splat_raster_forward_render(int P, int R, int W, int H, const float* background, const float* colors_precomp,
+                                const int* radii, void* geom, void* binning, void* image, float* out_color,
+                                float* out_depth, float* out_opacity, int* n_touched, void* stream) {
+    return forward_render_impl(P, R, W, H, background, colors_precomp, radii, geom, binning, image, out_color, out_depth,
+                               out_opacity, n_touched, nullptr, stream);
+}
+
+int splat_raster_forward_render_loss(int P, int R, int W, int H, const float* background, const float* colors_precomp,
+                                     const int* radii, void* geom, void* binning, void* image, float* out_color,
+                                     float* out_depth, float* out_opacity, int* n_touched,
+                                     const splat_raster_loss_desc* loss, void* stream) {
+    if (!loss) return SPLAT_ERR_ARG;
+    LossDesc L;
+    const int rc = loss_desc_from_abi(W, H, loss, &L);
+    if (rc != SPLAT_OK) return rc;
+    return forward_render_impl(P, R, W, H, background, colors_precomp, radii, geom, binning, image, out_color, out_depth,
+                               out_opacity, n_touched, &L, stream);
+}
+
+int splat_raster_loss_partials(int W, int H) {
+    if (W <= 0 || H <= 0) return 0;
+    const int tiles = grid_dim(W) * grid_dim(H), blocks = mapping_loss_blocks(W * H);
+    return tiles > blocks ? tiles : blocks;     // one workspace serves both the stand-alone and the fused loss
 }
 
 int splat_raster_backward(int P, int D, int M, int R, int W, int H, const float* background, const float* means3D,
@@ -385,8 +430,11 @@ int splat_raster_mapping_loss(int W, int H, const float* image, const float* dep
         return SPLAT_ERR_ARG;
     if ((reinterpret_cast<uintptr_t>(workspace) & 15u) != 0) return SPLAT_ERR_ARG;
     if (!initialization && (!exposure_a || !exposure_b)) return SPLAT_ERR_ARG;
-    launch_mapping_loss(W * H, image, depth, gt_image, gt_depth, exposure_a, exposure_b, alpha, rgb_boundary_threshold,
-                        initialization, workspace, out, dL_dimage, dL_ddepth, (cudaStream_t)stream);
+    LossDesc L;
+    L.gt_image = gt_image; L.gt_depth = gt_depth; L.exposure_a = exposure_a; L.exposure_b = exposure_b;
+    L.alpha = alpha; L.rgb_boundary_threshold = rgb_boundary_threshold; L.initialization = initialization;
+    L.workspace = workspace; L.out = out; L.dL_dimage = dL_dimage; L.dL_ddepth = dL_ddepth;
+    launch_mapping_loss(W * H, image, depth, L, (cudaStream_t)stream);
     g_launches += 1;
     SPLAT_CUDA_CHECK_LAUNCH();
     return SPLAT_OK;

@@ -3,6 +3,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include "state.h"
+#include "loss.cuh"
 
 namespace splat {
 
@@ -50,10 +51,7 @@ void launch_sort_pairs(uint32_t* k0, uint32_t* v0, uint32_t* k1, uint32_t* v1, i
                        cudaStream_t s, const RecordSink* sink = nullptr);
 // mapping_loss.cu
 int mapping_loss_blocks(int N);
-void launch_mapping_loss(int N, const float* image, const float* depth, const float* gt_image, const float* gt_depth,
-                         const float* exposure_a, const float* exposure_b, float alpha, float rgb_boundary_threshold,
-                         int initialization, float* workspace, float* out, float* dL_dimage, float* dL_ddepth,
-                         cudaStream_t s);
+void launch_mapping_loss(int N, const float* image, const float* depth, const LossDesc& loss, cudaStream_t s);
 // adam.cu
 constexpr int kAdamMaxSegments = 32;      // tensors per launch (kernel-parameter space)
 struct AdamSegment {
@@ -93,7 +91,8 @@ int launch_allreduce_multimem(float* multicast, int world, int rank, size_t coun
 // render.cu
 void launch_render_forward(int W, int H, int grid_x, int grid_y, uint2* ranges, const float* records,
                            const float* bg, float* final_T, uint32_t* n_contrib, float* out_color, float* out_depth,
-                           float* out_opacity, int* n_touched, const uint32_t* sort_error, cudaStream_t s);
+                           float* out_opacity, int* n_touched, const uint32_t* sort_error, const LossDesc* loss,
+                           cudaStream_t s);
 void launch_render_backward(int W, int H, int grid_x, int grid_y, const uint2* ranges, const float* records,
                             const float* bg, const float* final_T, const uint32_t* n_contrib, const float* dL_dpix,
                             const float* dL_dpix_depth, float* grad_accum, cudaStream_t s);

@@ -122,11 +122,17 @@ __device__ __forceinline__ int lds_volatile(uint32_t addr) {
 // and the LAST warp to do so re-arms the stage with the batch kFwdStages further on. A warp whose 32 pixels are all
 // saturated (or outside the image) keeps counting itself off without looking at the records; when all eight are in
 // that state nobody refills and everybody leaves (the reference's "whole tile done" exit, forward.cu:318-320).
+//
+// kLoss: the mapping loss that follows the rasterizer on every view of a mapping step
+// (thirdparty/monogs/utils/slam_utils.py:71-105) is evaluated in the epilogue, from the pixel's colour and depth still
+// in registers: dL/dimage and dL/ddepth are written next to the images, the loss sums are reduced per tile and
+// finished by the last CTA (loss.cuh). One launch less per view and no re-read of the rendered images.
+template <bool kLoss>
 __global__ void __launch_bounds__(SPLAT_TILE_PIXELS)
 render_forward_kernel(int W, int H, int grid_x, uint2* __restrict__ ranges, const float* __restrict__ records,
                       const float* __restrict__ bg, float* __restrict__ final_T, uint32_t* __restrict__ n_contrib,
                       float* __restrict__ out_color, float* __restrict__ out_depth, float* __restrict__ out_opacity,
-                      int* __restrict__ n_touched, const uint32_t* __restrict__ sort_error) {
+                      int* __restrict__ n_touched, const uint32_t* __restrict__ sort_error, LossDesc loss) {
     // an instance sort whose look-back gave up must not go unnoticed: fail the stream loudly
     if (blockIdx.x == 0 && threadIdx.x == 0 && sort_error != nullptr && *sort_error != 0u) {
         printf("splat_raster: tile sort look-back timed out\n");
@@ -291,13 +297,14 @@ render_forward_kernel(int W, int H, int grid_x, uint2* __restrict__ ranges, cons
         }
     }
 
+    const size_t HW = (size_t)H * W;
+    const float o0 = ffma(bg[0], T, C0), o1 = ffma(bg[1], T, C1), o2 = ffma(bg[2], T, C2);
     if (inside) {
         final_T[pix_id] = T;
         n_contrib[pix_id] = last_contributor;
-        const size_t HW = (size_t)H * W;
-        out_color[pix_id] = ffma(bg[0], T, C0);
-        out_color[HW + pix_id] = ffma(bg[1], T, C1);
-        out_color[2 * HW + pix_id] = ffma(bg[2], T, C2);
+        out_color[pix_id] = o0;
+        out_color[HW + pix_id] = o1;
+        out_color[2 * HW + pix_id] = o2;
         out_depth[pix_id] = Dp;
         out_opacity[pix_id] = fsub(1.0f, T);
     }
@@ -309,14 +316,29 @@ render_forward_kernel(int W, int H, int grid_x, uint2* __restrict__ ranges, cons
         const int issued = lds_volatile(issued_a);
         for (int k = b; k < issued; ++k) mbar_wait(&s_full[k % kFwdStages], (uint32_t)((k / kFwdStages) & 1));
     }
+
+    if constexpr (kLoss) {
+        const float ea = loss.initialization ? 1.0f : expf(loss.exposure_a[0]);
+        const float eb = loss.initialization ? 0.0f : loss.exposure_b[0];
+        const float w_rgb = loss.alpha / (3.0f * (float)HW), w_d = (1.0f - loss.alpha) / (float)HW;
+        float v[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+        if (inside) loss_pixel(loss, HW, (size_t)pix_id, o0, o1, o2, Dp, ea, eb, w_rgb, w_d, v);
+        loss_finish<SPLAT_TILE_PIXELS>(v, loss.workspace, loss.out, w_rgb, w_d);
+    }
 }
 
 void launch_render_forward(int W, int H, int grid_x, int grid_y, uint2* ranges, const float* records,
                            const float* bg, float* final_T, uint32_t* n_contrib, float* out_color, float* out_depth,
-                           float* out_opacity, int* n_touched, const uint32_t* sort_error, cudaStream_t s) {
-    render_forward_kernel<<<grid_x * grid_y, SPLAT_TILE_PIXELS, 0, s>>>(W, H, grid_x, ranges, records, bg, final_T,
-                                                                        n_contrib, out_color, out_depth, out_opacity,
-                                                                        n_touched, sort_error);
+                           float* out_opacity, int* n_touched, const uint32_t* sort_error, const LossDesc* loss,
+                           cudaStream_t s) {
+    if (loss != nullptr)
+        render_forward_kernel<true><<<grid_x * grid_y, SPLAT_TILE_PIXELS, 0, s>>>(
+            W, H, grid_x, ranges, records, bg, final_T, n_contrib, out_color, out_depth, out_opacity, n_touched,
+            sort_error, *loss);
+    else
+        render_forward_kernel<false><<<grid_x * grid_y, SPLAT_TILE_PIXELS, 0, s>>>(
+            W, H, grid_x, ranges, records, bg, final_T, n_contrib, out_color, out_depth, out_opacity, n_touched,
+            sort_error, LossDesc());
 }
 
 // =====================================================================================================

@@ -51,8 +51,31 @@ class GaussianRasterizationSettings(NamedTuple):
 
 def rasterize_gaussians(means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp, theta, rho,
                         raster_settings):
+    req = getattr(_pending_loss, "request", None)
+    if req is not None and req.loss is None:
+        # a mapping loss was attached to this render (mapping_loss.attach_loss): it is evaluated in the epilogue of
+        # the forward renderer and comes back as a sixth, differentiable output that is handed to the requester
+        color, radii, depth, opacity, n_touched, loss = _RasterizeGaussiansLoss.apply(
+            means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp, theta, rho,
+            req.exposure_a, req.exposure_b, raster_settings, req)
+        req.loss = loss
+        return color, radii, depth, opacity, n_touched
     return _RasterizeGaussians.apply(means3D, means2D, sh, colors_precomp, opacities, scales, rotations,
                                      cov3Ds_precomp, theta, rho, raster_settings)
+
+
+_pending_loss = threading.local()      # .request: the LossRequest the next render of this thread should evaluate
+
+
+class LossRequest:
+    """What `mapping_loss.attach_loss` leaves for the next render of the calling thread."""
+
+    def __init__(self, gt_image, gt_depth, exposure_a, exposure_b, alpha, rgb_boundary_threshold, initialization):
+        self.gt_image, self.gt_depth = gt_image, gt_depth
+        self.exposure_a, self.exposure_b = exposure_a, exposure_b
+        self.alpha, self.rgb_boundary_threshold = float(alpha), float(rgb_boundary_threshold)
+        self.initialization = bool(initialization)
+        self.loss = None            # set by the render: 0-dim tensor, differentiable
 
 
 class _PinnedInt:
@@ -73,9 +96,14 @@ class _PinnedInt:
         return t
 
 
-def _forward_impl(S, means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp):
+_loss_workspaces = {}     # (device index, stream handle) -> zeroed ticket + per-tile partials, reused call after call
+
+
+def _forward_impl(S, means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp, loss=None):
     """Equivalent of `_C.rasterize_gaussians` (DGR/rasterize_points.cu:35-122): returns
-    (num_rendered, color, radii, geomBuffer, binningBuffer, imgBuffer, depth, opacity, n_touched)."""
+    (num_rendered, color, radii, geomBuffer, binningBuffer, imgBuffer, depth, opacity, n_touched).
+    With `loss` (a LossRequest) the mapping loss is evaluated in the render epilogue and the tuple grows by
+    (loss sums[5], dL/dimage, dL/ddepth)."""
     if means3D.ndimension() != 2 or means3D.size(1) != 3:
         raise RuntimeError("means3D must have dimensions (num_points, 3)")
     L = _cabi.lib()
@@ -126,14 +154,40 @@ def _forward_impl(S, means3D, sh, colors_precomp, opacities, scales, rotations, 
                 _cabi.check(L.splat_raster_forward_wait(), "forward_wait")   # returns while the depth sort still runs
                 rendered = int(host_R.item())
             binning = torch.empty((L.splat_raster_binning_bytes(rendered),), dtype=torch.uint8, device=dev)
-            _cabi.check(L.splat_raster_forward_render(
-                P, rendered, W, H, _cabi.ptr(bg), _cabi.ptr(colors_precomp), _cabi.ptr(radii), geom.data_ptr(),
-                binning.data_ptr(), image.data_ptr(), out_color.data_ptr(), out_depth.data_ptr(),
-                out_opacity.data_ptr(), _cabi.ptr(n_touched), stream), "forward_render")
+            common = (P, rendered, W, H, _cabi.ptr(bg), _cabi.ptr(colors_precomp), _cabi.ptr(radii), geom.data_ptr(),
+                      binning.data_ptr(), image.data_ptr(), out_color.data_ptr(), out_depth.data_ptr(),
+                      out_opacity.data_ptr(), _cabi.ptr(n_touched))
+            extra = ()
+            if loss is None:
+                _cabi.check(L.splat_raster_forward_render(*common, stream), "forward_render")
+            else:
+                gt_image = _cabi.require_cuda("gt_image", loss.gt_image)
+                gt_depth = _cabi.require_cuda("gt_depth", loss.gt_depth)
+                if gt_image.numel() != 3 * H * W or gt_depth.numel() != H * W:
+                    raise RuntimeError("gt_image / gt_depth do not match the rendered image shape")
+                ea = eb = None
+                if not loss.initialization:
+                    ea = _cabi.require_cuda("exposure_a", loss.exposure_a.detach().reshape(-1))
+                    eb = _cabi.require_cuda("exposure_b", loss.exposure_b.detach().reshape(-1))
+                words = 4 + 4 * L.splat_raster_loss_partials(W, H)
+                ws = _loss_workspaces.get((dev.index, stream))
+                if ws is None or ws.numel() < words:
+                    # zeroed once; the kernel hands the ticket word back as 0, and calls on one stream are ordered
+                    ws = _loss_workspaces[(dev.index, stream)] = torch.zeros(words, **f32)
+                sums = torch.empty(5, **f32)
+                dimg = torch.empty((3, H, W), **f32)
+                ddepth = torch.empty((1, H, W), **f32)
+                desc = _cabi._LossDesc(gt_image.data_ptr(), gt_depth.data_ptr(), _cabi.ptr(ea), _cabi.ptr(eb),
+                                       loss.alpha, loss.rgb_boundary_threshold, int(loss.initialization),
+                                       ws.data_ptr(), sums.data_ptr(), dimg.data_ptr(), ddepth.data_ptr())
+                import ctypes
+                _cabi.check(L.splat_raster_forward_render_loss(*common, ctypes.byref(desc), stream),
+                            "forward_render_loss")
+                extra = (sums, dimg, ddepth)
         finally:
             if was_debug is not None:
                 _cabi.set_debug(was_debug)
-    return rendered, out_color, radii, geom, binning, image, out_depth, out_opacity, n_touched
+    return (rendered, out_color, radii, geom, binning, image, out_depth, out_opacity, n_touched) + extra
 
 
 _debug_fail_stage = -1      # tests set this to a stage index to exercise the error path of debug=True
@@ -276,6 +330,71 @@ class _RasterizeGaussians(torch.autograd.Function):
         grads = (grad_means3D, grad_means2D, grad_sh, grad_colors_precomp, grad_opacities, grad_scales, grad_rotations,
                  grad_cov3Ds_precomp, grad_theta, grad_rho, None)
         return grads
+
+
+class _RasterizeGaussiansLoss(torch.autograd.Function):
+    """`_RasterizeGaussians` plus the mapping loss of the view, evaluated in the epilogue of the forward renderer
+    (thirdparty/monogs/utils/slam_utils.py:71-105). Extra inputs: exposure_a, exposure_b (differentiable) and the
+    LossRequest; extra output: the loss. Backward adds `grad_loss * dL/dimage` (and `* dL/ddepth`) to whatever arrives
+    for color / depth directly."""
+
+    @staticmethod
+    def forward(ctx, means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp, theta, rho,
+                exposure_a, exposure_b, raster_settings, req):
+        def dense(name, t):
+            return _cabi.require_cuda(name, t) if t.numel() != 0 else t
+        if means3D.ndimension() != 2 or means3D.size(1) != 3:
+            raise RuntimeError("means3D must have dimensions (num_points, 3)")
+        means3D = _cabi.require_cuda("means3D", means3D)
+        sh, colors_precomp = dense("sh", sh), dense("colors_precomp", colors_precomp)
+        opacities, scales, rotations = dense("opacities", opacities), dense("scales", scales), dense("rotations", rotations)
+        cov3Ds_precomp = dense("cov3Ds_precomp", cov3Ds_precomp)
+        res = _forward_impl(raster_settings, means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,
+                            loss=req)
+        num_rendered, color, radii, geomBuffer, binningBuffer, imgBuffer, depth, opacity, n_touched, sums, dimg, ddepth = res
+        ctx.raster_settings = raster_settings
+        ctx.num_rendered = num_rendered
+        ctx.initialization = req.initialization
+        ctx.exposure_shapes = (None if exposure_a is None else exposure_a.shape,
+                               None if exposure_b is None else exposure_b.shape)
+        ctx.save_for_backward(colors_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh, geomBuffer,
+                              binningBuffer, imgBuffer, sums, dimg, ddepth)
+        ctx.mark_non_differentiable(radii, n_touched)
+        ctx.set_materialize_grads(False)
+        return color, radii, depth, opacity, n_touched, sums[0]
+
+    @staticmethod
+    def backward(ctx, grad_out_color, grad_out_radii, grad_out_depth, grad_out_opacity, grad_n_touched, grad_loss):
+        S = ctx.raster_settings
+        (colors_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh, geomBuffer, binningBuffer, imgBuffer,
+         sums, dimg, ddepth) = ctx.saved_tensors
+        dev = means3D.device
+        H, W = int(S.image_height), int(S.image_width)
+        up_c, up_d = grad_out_color, grad_out_depth
+        ga = gb = None
+        if grad_loss is not None:
+            up_c = dimg * grad_loss if up_c is None else up_c + dimg * grad_loss
+            up_d = ddepth * grad_loss if up_d is None else up_d + ddepth * grad_loss
+            if not ctx.initialization:
+                ga = (grad_loss * sums[3]).reshape(ctx.exposure_shapes[0])
+                gb = (grad_loss * sums[4]).reshape(ctx.exposure_shapes[1])
+        if up_c is None:
+            up_c = torch.zeros((3, H, W), dtype=torch.float32, device=dev)
+        if up_d is None:
+            up_d = torch.zeros((1, H, W), dtype=torch.float32, device=dev)
+        ng = ctx.needs_input_grad
+        needs = dict(means3D=ng[0], means2D=ng[1], sh=ng[2], colors=ng[3], opacity=ng[4],
+                     scale_rot=ng[5] or ng[6], cov3D=ng[7])
+        (grad_means2D, grad_colors_precomp, grad_opacities, grad_means3D, grad_cov3Ds_precomp, grad_sh, grad_scales,
+         grad_rotations, grad_tau) = _backward_impl(S, means3D, radii, colors_precomp, scales, rotations, cov3Ds_precomp,
+                                                    up_c, up_d, sh, geomBuffer, ctx.num_rendered, binningBuffer,
+                                                    imgBuffer, needs)
+        grad_rho = grad_tau[:3].view(1, -1)
+        grad_theta = grad_tau[3:].view(1, -1)
+        if not ng[2]:
+            grad_sh = None
+        return (grad_means3D, grad_means2D, grad_sh, grad_colors_precomp, grad_opacities, grad_scales, grad_rotations,
+                grad_cov3Ds_precomp, grad_theta, grad_rho, ga, gb, None, None)
 
 
 class GaussianRasterizer(nn.Module):

@@ -28,6 +28,13 @@ class _Views(ctypes.Structure):
                                         "point_list", "ranges", "final_T", "n_contrib")]
 
 
+class _LossDesc(ctypes.Structure):
+    """splat_raster_loss_desc (include/splat_raster.h)."""
+    _fields_ = [("gt_image", c_void_p), ("gt_depth", c_void_p), ("exposure_a", c_void_p), ("exposure_b", c_void_p),
+                ("alpha", c_float), ("rgb_boundary_threshold", c_float), ("initialization", c_int),
+                ("workspace", c_void_p), ("out", c_void_p), ("dL_dimage", c_void_p), ("dL_ddepth", c_void_p)]
+
+
 EXPORTS = (
     "splat_raster_abi_version", "splat_raster_geom_bytes", "splat_raster_image_bytes", "splat_raster_binning_bytes",
     "splat_raster_forward_preprocess", "splat_raster_forward_wait", "splat_raster_forward_render", "splat_raster_backward",
@@ -39,7 +46,7 @@ EXPORTS = (
     "splat_raster_deform_points", "splat_raster_activations_forward", "splat_raster_activations_backward", "splat_raster_priority_lanes",
     "splat_raster_backward_noalloc", "splat_raster_set_debug", "splat_raster_last_failed_stage",
     "splat_raster_debug_sync_count", "splat_raster_allreduce_peer", "splat_raster_allreduce_multimem",
-    "splat_raster_keep_sort_output",
+    "splat_raster_keep_sort_output", "splat_raster_forward_render_loss", "splat_raster_loss_partials",
 )
 
 
@@ -67,6 +74,10 @@ def lib() -> ctypes.CDLL:
     L.splat_raster_forward_wait.argtypes = []
     L.splat_raster_forward_render.restype = c_int
     L.splat_raster_forward_render.argtypes = [c_int] * 4 + [P] * 11
+    L.splat_raster_forward_render_loss.restype = c_int
+    L.splat_raster_forward_render_loss.argtypes = [c_int] * 4 + [P] * 10 + [POINTER(_LossDesc), P]
+    L.splat_raster_loss_partials.restype = c_int
+    L.splat_raster_loss_partials.argtypes = [c_int, c_int]
     L.splat_raster_backward.restype = c_int
     L.splat_raster_backward.argtypes = [c_int] * 6 + [P, P, P, P, P, c_float, P, P, P, P, P, P, c_float, c_float] + [P] * 17
     L.splat_raster_mark_visible.restype = c_int

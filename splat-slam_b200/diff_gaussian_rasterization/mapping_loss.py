@@ -117,6 +117,49 @@ def invalidate_depth_cache(viewpoint):
         viewpoint._depth_cuda = None
 
 
+class attach_loss:
+    """Evaluate the mapping loss of a view INSIDE its render instead of after it.
+
+        with attach_loss(config, viewpoint, initialization=False) as fused:
+            render_pkg = render(viewpoint, gaussians, pipe, background)     # any code that ends up in GaussianRasterizer
+        loss_mapping += fused.loss          # == get_loss_mapping(config, image, depth, viewpoint, opacity, ...)
+
+    The next `GaussianRasterizer` call of this thread computes the loss in the epilogue of its forward kernel, from the
+    pixel values still in registers, and its backward uses the loss gradients directly: one launch, one pass over the
+    rendered images and the Python glue of a second autograd node less per view. `image` and `depth` of the render are
+    still returned and still differentiable, so other terms can use them. Same value and gradients as
+    `get_loss_mapping` (ssim_loss: False path, thirdparty/monogs/utils/slam_utils.py:71-105)."""
+
+    def __init__(self, config, viewpoint, initialization=False):
+        training = config["Training"]
+        if training.get("ssim_loss", False):
+            raise NotImplementedError("the fused loss covers the ssim_loss: False path only (configs/splat_slam.yaml:36)")
+        self._args = (training["alpha"] if "alpha" in training else 0.95, training["rgb_boundary_threshold"])
+        self._viewpoint, self._initialization = viewpoint, initialization
+        self._request = None
+
+    def __enter__(self):
+        from . import LossRequest, _pending_loss
+        vp = self._viewpoint
+        gt_image = vp.original_image if vp.original_image.is_cuda else vp.original_image.cuda()
+        self._request = LossRequest(gt_image, _device_depth(vp, gt_image.device), vp.exposure_a, vp.exposure_b,
+                                    self._args[0], self._args[1], self._initialization)
+        self._previous = getattr(_pending_loss, "request", None)
+        _pending_loss.request = self._request
+        return self
+
+    def __exit__(self, *exc):
+        from . import _pending_loss
+        _pending_loss.request = self._previous
+        return False
+
+    @property
+    def loss(self):
+        if self._request is None or self._request.loss is None:
+            raise RuntimeError("attach_loss: no render ran inside the with-block")
+        return self._request.loss
+
+
 def get_loss_mapping(config, image, depth, viewpoint, opacity, initialization=False):
     """Drop-in for thirdparty/monogs/utils/slam_utils.py:71-78 (+ get_loss_mapping_rgbd :81-105)."""
     training = config["Training"]

@@ -166,10 +166,21 @@ def test_stress_footprint_binning_stays_bit_exact(kind):
     # per-Gaussian chain agrees for all but a handful of ill-conditioned Gaussians.
     for k in ("means2D", "shs", "opacities"):
         assert T.rel_err(a["grad_" + k], b["grad_" + k]) <= T.GRAD_RTOL, k
+    # The data behind that relaxation, measured here and printed into the log: the reference against ITSELF (a second
+    # run on the same inputs; float atomics reorder its sums) on the same three tensors.
+    b2 = T.run_module(T.load_ref(), case)
     for k in ("means3D", "scales", "rotations"):
-        ga, gb = a["grad_" + k].cpu(), b["grad_" + k].cpu()
-        bad = ((ga - gb).abs().amax(1) > T.GRAD_RTOL * gb.abs().max()).float().mean()
+        ga, gb, gb2 = a["grad_" + k].cpu(), b["grad_" + k].cpu(), b2["grad_" + k].cpu()
+        scale = T.GRAD_RTOL * gb.abs().max()
+        bad = ((ga - gb).abs().amax(1) > scale).float().mean()
+        ref_bad = ((gb2 - gb).abs().amax(1) > scale).float().mean()
+        worst_rows = (gb2 - gb).abs().amax(1).topk(min(8, gb.shape[0])).indices
+        ref_rel = ((gb2 - gb).abs().amax(1)[worst_rows] / gb.abs().amax(1)[worst_rows].clamp_min(1e-30)).max()
+        print(f"needles grad_{k}: ours-vs-ref rows beyond 1e-3 of max: {float(bad):.5f}; "
+              f"ref-vs-ref rows beyond: {float(ref_bad):.5f}; ref-vs-ref worst per-row relative spread: {float(ref_rel):.3f}")
         assert float(bad) <= 0.005, (k, float(bad))
+        # ours is allowed to differ from the reference where (and by about as much as) the reference differs from itself
+        assert float(bad) <= 10 * float(ref_bad) + 0.001, (k, float(bad), float(ref_bad))
 
 
 # ---- edge cases -------------------------------------------------------------------------------------------
