@@ -3,8 +3,8 @@
   reference : the compiled reference rasterizer (oracle/_ref/ref_dgr) driven the way the reference drives it —
               activations inside every render call, torch mapping loss per view, isotropic loss, ONE backward over the
               summed loss, the boolean-index densification loop, torch.optim.Adam for the Gaussians and the keyframes;
-  ours      : fused activations once per iteration, this library's rasterizer with the views on three streams, fused
-              mapping loss, per-view backward, fused densification stats / visibility, GaussianAdam for both optimizers.
+  ours      : fused activations once per iteration, this library's rasterizer with the views on five streams, the
+              mapping loss evaluated inside each render (LOSS=kernel: stand-alone fused kernel), per-view backward, fused densification stats / visibility, GaussianAdam for both optimizers.
 
     gpurun -- 'python tests/perf/bench_iteration.py'          # prints ms per iteration for each arm
 """
@@ -23,7 +23,7 @@ from diff_gaussian_rasterization import synthetic as syn  # noqa: E402
 from diff_gaussian_rasterization.activations import fused_activations  # noqa: E402
 from diff_gaussian_rasterization.adam import GaussianAdam  # noqa: E402
 from diff_gaussian_rasterization.densify import add_densification_stats_window, occ_aware_visibility  # noqa: E402
-from diff_gaussian_rasterization.mapping_loss import fused_mapping_loss  # noqa: E402
+from diff_gaussian_rasterization.mapping_loss import attach_loss, fused_mapping_loss  # noqa: E402
 from diff_gaussian_rasterization.window import ViewStreams  # noqa: E402
 from oracle.densify import densification_stats_window  # noqa: E402
 from oracle.mapping_loss import mapping_loss  # noqa: E402
@@ -61,6 +61,7 @@ def make_state(adam_cls):
         vp.exposure_b = torch.nn.Parameter(torch.zeros(1, device=dev))
         vp.gt_image = torch.rand(3, H, W, generator=gen).to(dev)
         vp.gt_depth = (1.0 + 3.0 * torch.rand(1, H, W, generator=gen)).to(dev)
+        vp.original_image, vp.depth = vp.gt_image, vp.gt_depth[0]      # the names the reference's viewpoints use
         for prm, lr in ((vp.theta, 3e-3), (vp.rho, 1e-3), (vp.exposure_a, 0.01), (vp.exposure_b, 0.01)):
             kf_params.append({"params": [prm], "lr": lr})
         st.views.append(vp)
@@ -105,7 +106,9 @@ def iteration_reference(st, mod, do_step=True):
     return vis
 
 
-streams = ViewStreams(dev, 3)
+streams = ViewStreams(dev, int(os.environ.get("STREAMS", 5)))
+LOSS_IN_RENDER = os.environ.get("LOSS", "attached") == "attached"     # LOSS=kernel: the stand-alone fused loss kernel
+CFG = {"Training": {"alpha": 0.95, "rgb_boundary_threshold": 0.01, "ssim_loss": False}}
 
 
 def iteration_ours(st, mod, do_step=True):
@@ -118,10 +121,19 @@ def iteration_ours(st, mod, do_step=True):
     for k, vp in enumerate(st.views):
         with streams.view(k):
             means2D = torch.zeros_like(st.xyz, requires_grad=True)
-            color, radii, depth, opacity, n_touched = mod.GaussianRasterizer(settings(mod, st, vp))(
-                means3D=st.xyz, means2D=means2D, shs=st.f_dc, opacities=leaves[2], scales=leaves[0], rotations=leaves[1],
-                theta=vp.theta, rho=vp.rho)
-            fused_mapping_loss(color, depth, vp.exposure_a, vp.exposure_b, vp.gt_image, vp.gt_depth, 0.95, 0.01).backward()
+
+            def render():
+                return mod.GaussianRasterizer(settings(mod, st, vp))(
+                    means3D=st.xyz, means2D=means2D, shs=st.f_dc, opacities=leaves[2], scales=leaves[0],
+                    rotations=leaves[1], theta=vp.theta, rho=vp.rho)
+
+            if LOSS_IN_RENDER:
+                with attach_loss(CFG, vp) as fused:
+                    color, radii, depth, opacity, n_touched = render()
+                fused.loss.backward()
+            else:
+                color, radii, depth, opacity, n_touched = render()
+                fused_mapping_loss(color, depth, vp.exposure_a, vp.exposure_b, vp.gt_image, vp.gt_depth, 0.95, 0.01).backward()
             vsp.append(means2D); radii_acm.append(radii); nt_acm.append(n_touched)
     streams.join()
     iso = 10 * torch.abs(scales - scales.mean(dim=1).view(-1, 1)).mean()
