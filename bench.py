@@ -77,6 +77,9 @@ def parse():
     ap.add_argument("--no-extras", action="store_true", help="skip the single-stream legs, the strong sub-record and "
                     "the other BASELINE configs (only the main value / e2e legs and the stage profile)")
     ap.add_argument("--verify", action="store_true")
+    ap.add_argument("--view-offset", type=int, default=0,
+                    help="first view id of rank 0 (weak scaling gives rank r the views offset + r*views ...): lets one "
+                         "GPU time the view set another rank gets")
     ap.add_argument("--exchange", default="auto", choices=["auto", "nccl", "peer"],
                     help="gradient exchange at N > 1: this library's peer-memory all-reduce kernel or NCCL")
     ap.add_argument("--priority-lanes", type=int, default=1, help="1: short kernels on a high-priority side stream")
@@ -169,7 +172,7 @@ class Workload:
         else:
             self.params, self.flat = shared.params, shared.flat
         if scaling == "weak":
-            self.view_ids = [rank * args.views + i for i in range(args.views)]
+            self.view_ids = [args.view_offset + rank * args.views + i for i in range(args.views)]
             self.global_views = args.views * world
         else:
             self.view_ids = partition_views(args.views, world, rank)
@@ -505,6 +508,26 @@ def main():
         extras["exchange"] = {"kind": wl.flat.exchange_kind, "bytes": wl.flat.flat.numel() * 4, "ms": ms_x,
                               "share_of_step": ms_x / ms_step,
                               "note": "issued after the rank's last backward; nothing of the step is left to hide it"}
+        # ---- how evenly the views load the ranks: each rank's step WITHOUT the exchange (the ranks render different
+        # poses, so their instance counts differ); the step of the job is the slowest rank's plus the exchange
+        ex, wl.flat.all_reduce = wl.flat.all_reduce, (lambda group=None: None)
+        for _ in range(2):
+            wl.step_resident()
+        torch.cuda.synchronize(device)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(5):
+            wl.step_resident()
+        e1.record()
+        torch.cuda.synchronize(device)
+        wl.flat.all_reduce = ex
+        mine = torch.tensor([e0.elapsed_time(e1) / 5], device=device)
+        every = [torch.zeros_like(mine) for _ in range(ref_world)]
+        dist.all_gather(every, mine)
+        local = [float(t.item()) for t in every]
+        extras["rank_local_ms_per_step"] = {"per_rank": local, "max": max(local), "mean": sum(local) / len(local),
+                                            "note": "without the exchange; weak scaling gives every rank its own 10 "
+                                                    "poses, so the work per rank differs by the poses' instance counts"}
     # ---- what an unmodified caller gets: every view on the caller's stream, no priority lanes
     if kind == "ours" and not args.no_extras and n_streams > 1:
         wl.set_streams(1, False)

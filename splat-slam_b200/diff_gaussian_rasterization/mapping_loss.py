@@ -1,7 +1,8 @@
 """Fused mapping loss (forward + backward in one CUDA pass) for the views a mapping step renders.
 
 Mirrors `get_loss_mapping(config, image, depth, viewpoint, opacity, initialization=False)` of the reference
-(thirdparty/monogs/utils/slam_utils.py:71-105, the `ssim_loss: False` path that configs/splat_slam.yaml:36 selects):
+(thirdparty/monogs/utils/slam_utils.py:71-105; the `ssim_loss: False` path that configs/splat_slam.yaml:36 selects is
+the fused kernel, the SSIM term of `ssim_loss: True` is added with torch ops):
 same arguments, same value, same gradients w.r.t. `image`, `depth`, `viewpoint.exposure_a`, `viewpoint.exposure_b`,
 but one kernel instead of ~10 elementwise/reduction kernels, and the ground-truth depth is uploaded once per
 `viewpoint.depth` array instead of on every call (the reference does `torch.from_numpy(viewpoint.depth).to(device)`
@@ -160,16 +161,50 @@ class attach_loss:
         return self._request.loss
 
 
+def _ssim(img1, img2, window_size=11):
+    """SSIM exactly as thirdparty/gaussian_splatting/utils/loss_utils.py:37-99 (11x11 Gaussian window, sigma 1.5, zero
+    padding, mean over the map), on torch ops: this branch is off in the shipped configuration."""
+    import math
+
+    import torch.nn.functional as F
+    channel = img1.size(-3)
+    g = torch.tensor([math.exp(-((x - window_size // 2) ** 2) / float(2 * 1.5 ** 2)) for x in range(window_size)])
+    g = (g / g.sum()).unsqueeze(1)
+    window = g.mm(g.t()).float().unsqueeze(0).unsqueeze(0).expand(channel, 1, window_size, window_size).contiguous()
+    window = window.to(img1)
+    pad = window_size // 2
+    mu1 = F.conv2d(img1, window, padding=pad, groups=channel)
+    mu2 = F.conv2d(img2, window, padding=pad, groups=channel)
+    mu1_sq, mu2_sq, mu1_mu2 = mu1.pow(2), mu2.pow(2), mu1 * mu2
+    sigma1_sq = F.conv2d(img1 * img1, window, padding=pad, groups=channel) - mu1_sq
+    sigma2_sq = F.conv2d(img2 * img2, window, padding=pad, groups=channel) - mu2_sq
+    sigma12 = F.conv2d(img1 * img2, window, padding=pad, groups=channel) - mu1_mu2
+    C1, C2 = 0.01 ** 2, 0.03 ** 2
+    ssim_map = ((2 * mu1_mu2 + C1) * (2 * sigma12 + C2)) / ((mu1_sq + mu2_sq + C1) * (sigma1_sq + sigma2_sq + C2))
+    return ssim_map.mean()
+
+
 def get_loss_mapping(config, image, depth, viewpoint, opacity, initialization=False):
-    """Drop-in for thirdparty/monogs/utils/slam_utils.py:71-78 (+ get_loss_mapping_rgbd :81-105)."""
+    """Drop-in for thirdparty/monogs/utils/slam_utils.py:71-78 (+ get_loss_mapping_rgbd :81-105).
+
+    `ssim_loss: False` (configs/splat_slam.yaml:36) is one fused kernel. With `ssim_loss: True` the reference's
+    loss is alpha * ((1-h) * mean l1_rgb + h * (1 - ssim(image_ab, gt))) + (1-alpha) * mean l1_depth with
+    h = config["opt_params"]["lambda_dssim"] (slam_utils.py:91-98): the two L1 terms still come from the fused kernel
+    (called with the equivalent mixing weight and rescaled), the SSIM term is added with torch ops."""
     training = config["Training"]
-    if training.get("ssim_loss", False):
-        raise NotImplementedError("fused mapping loss covers the ssim_loss: False path only (configs/splat_slam.yaml:36)")
     alpha = training["alpha"] if "alpha" in training else 0.95
     thr = training["rgb_boundary_threshold"]
     gt_image = viewpoint.original_image
     if not gt_image.is_cuda:
         gt_image = gt_image.cuda()
     gt_depth = _device_depth(viewpoint, image.device)
-    return fused_mapping_loss(image, depth, viewpoint.exposure_a, viewpoint.exposure_b, gt_image, gt_depth, alpha, thr,
-                              initialization)
+    if not training.get("ssim_loss", False):
+        return fused_mapping_loss(image, depth, viewpoint.exposure_a, viewpoint.exposure_b, gt_image, gt_depth, alpha,
+                                  thr, initialization)
+    h = config["opt_params"]["lambda_dssim"]
+    # alpha (1-h) A + (1-alpha) D  =  s * (alpha' A + (1-alpha') D)
+    s = alpha * (1.0 - h) + (1.0 - alpha)
+    l1 = fused_mapping_loss(image, depth, viewpoint.exposure_a, viewpoint.exposure_b, gt_image, gt_depth,
+                            alpha * (1.0 - h) / s, thr, initialization)
+    image_ab = image if initialization else torch.exp(viewpoint.exposure_a) * image + viewpoint.exposure_b
+    return s * l1 + alpha * h * (1.0 - _ssim(image_ab, gt_image))

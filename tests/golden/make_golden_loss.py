@@ -20,12 +20,13 @@ from oracle.mapping_loss import synthetic_loss_case  # noqa: E402
 
 out = {}
 for name, (H, W, seed, alpha, init) in {"a": (48, 64, 0, 0.8, False), "b": (70, 100, 1, 0.95, False),
-                                        "init": (48, 64, 2, 0.8, True)}.items():
+                                        "init": (48, 64, 2, 0.8, True), "ssim": (48, 64, 3, 0.8, False)}.items():
     c = synthetic_loss_case(H, W, seed)
     leaves = {k: c[k].clone().requires_grad_(True) for k in ("image", "depth", "exposure_a", "exposure_b")}
     vp = types.SimpleNamespace(original_image=c["gt_image"], depth=c["gt_depth"][0].numpy(),
                                exposure_a=leaves["exposure_a"], exposure_b=leaves["exposure_b"])
-    cfg = {"Training": {"alpha": alpha, "rgb_boundary_threshold": 0.01, "ssim_loss": False}}
+    cfg = {"Training": {"alpha": alpha, "rgb_boundary_threshold": 0.01, "ssim_loss": name == "ssim"},
+           "opt_params": {"lambda_dssim": 0.2}}
     loss = get_loss_mapping(cfg, leaves["image"], leaves["depth"], vp, None, initialization=init)
     loss.backward()
     out[name] = dict(H=H, W=W, seed=seed, alpha=alpha, initialization=init, loss=loss.detach(),
