@@ -317,7 +317,7 @@ int forward_render_impl(int P, int R, int W, int H, const float* background, con
     s = caller;
     SPLAT_CUDA_CHECK_LAUNCH();
     prof_begin(ST_RENDER_FWD, s);
-    launch_render_forward(W, H, gx, gy, im.ranges, b.records, background, im.final_T, im.n_contrib, out_color,
+    launch_render_forward(W, H, gx, gy, im.ranges, b.records, P < kWarpMaskMaxGaussians ? 1 : 0, background, im.final_T, im.n_contrib, out_color,
                           out_depth, out_opacity, n_touched, R > 0 ? sort_error_flag(b.sort_scratch) : nullptr, loss, s);
     SPLAT_STAGE_END(ST_RENDER_FWD, s, 1);
     SPLAT_CUDA_CHECK_LAUNCH();
@@ -380,7 +380,7 @@ int splat_raster_backward(int P, int D, int M, int R, int W, int H, const float*
     if (e != cudaSuccess) return (int)e;
     if (R > 0) {
         prof_begin(ST_RENDER_BWD, s);
-        launch_render_backward(W, H, gx, gy, im.ranges, b.records, background, im.final_T, im.n_contrib, dL_dout_color,
+        launch_render_backward(W, H, gx, gy, im.ranges, b.records, P < kWarpMaskMaxGaussians ? 1 : 0, background, im.final_T, im.n_contrib, dL_dout_color,
                                dL_dout_depth, grad_scratch, s);
         SPLAT_STAGE_END(ST_RENDER_BWD, s, 1);
         SPLAT_CUDA_CHECK_LAUNCH();
@@ -670,7 +670,7 @@ int splat_raster_backward_noalloc(int P, int D, int M, int R, int W, int H, cons
     e = cudaMemsetAsync(scratch, 0, sizeof(float) * SPLAT_GRAD_FLOATS * (size_t)P, s);
     if (e != cudaSuccess) return (int)e;
     if (R > 0) {
-        launch_render_backward(W, H, gx, gy, im.ranges, b.records, background, im.final_T, im.n_contrib, dL_dout_color,
+        launch_render_backward(W, H, gx, gy, im.ranges, b.records, P < kWarpMaskMaxGaussians ? 1 : 0, background, im.final_T, im.n_contrib, dL_dout_color,
                                dL_dout_depth, scratch, s);
         g_launches += 1;
         SPLAT_CUDA_CHECK_LAUNCH();

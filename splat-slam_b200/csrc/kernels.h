@@ -89,12 +89,15 @@ constexpr int kMaxPeerRanks = 8;          // GPUs of one NVSwitch node
 int launch_allreduce_peer(float* const* buffers, int world, int rank, size_t count, cudaStream_t s);      // -> launches, < 0 unsupported
 int launch_allreduce_multimem(float* multicast, int world, int rank, size_t count, cudaStream_t s);       // -> launches
 // render.cu
-void launch_render_forward(int W, int H, int grid_x, int grid_y, uint2* ranges, const float* records,
+// warp_mask: the forward marks, in bits 24..31 of every record's id word, which warps of the tile blended the instance,
+// and the backward lists instances by that mask (needs ids < 2^24; 0 = footprint test in both)
+constexpr int kWarpMaskMaxGaussians = 1 << 24;
+void launch_render_forward(int W, int H, int grid_x, int grid_y, uint2* ranges, float* records, int warp_mask,
                            const float* bg, float* final_T, uint32_t* n_contrib, float* out_color, float* out_depth,
                            float* out_opacity, int* n_touched, const uint32_t* sort_error, const LossDesc* loss,
                            cudaStream_t s);
 void launch_render_backward(int W, int H, int grid_x, int grid_y, const uint2* ranges, const float* records,
-                            const float* bg, const float* final_T, const uint32_t* n_contrib, const float* dL_dpix,
+                            int warp_mask, const float* bg, const float* final_T, const uint32_t* n_contrib, const float* dL_dpix,
                             const float* dL_dpix_depth, float* grad_accum, cudaStream_t s);
 
 }  // namespace splat

@@ -127,9 +127,15 @@ __device__ __forceinline__ int lds_volatile(uint32_t addr) {
 // (thirdparty/monogs/utils/slam_utils.py:71-105) is evaluated in the epilogue, from the pixel's colour and depth still
 // in registers: dL/dimage and dL/ddepth are written next to the images, the loss sums are reduced per tile and
 // finished by the last CTA (loss.cuh). One launch less per view and no re-read of the rendered images.
+// lane 0: set bit `bit` of the id word of a record in GLOBAL memory when `on` (see the warp mask below)
+__device__ __forceinline__ void mark_record(uint32_t* id_word, uint32_t bit, uint32_t lane, bool on) {
+    asm volatile("{\n\t.reg .pred p, q;\n\tsetp.ne.u32 q, %1, 0;\n\tsetp.eq.and.u32 p, %0, 0, q;\n\t@p red.global.or.b32 [%2], %3;\n\t}"
+                 ::"r"(lane), "r"((uint32_t)on), "l"(id_word), "r"(bit) : "memory");
+}
+
 template <bool kLoss>
 __global__ void __launch_bounds__(SPLAT_TILE_PIXELS)
-render_forward_kernel(int W, int H, int grid_x, uint2* __restrict__ ranges, const float* __restrict__ records,
+render_forward_kernel(int W, int H, int grid_x, uint2* __restrict__ ranges, float* __restrict__ records, int warp_mask,
                       const float* __restrict__ bg, float* __restrict__ final_T, uint32_t* __restrict__ n_contrib,
                       float* __restrict__ out_color, float* __restrict__ out_depth, float* __restrict__ out_opacity,
                       int* __restrict__ n_touched, const uint32_t* __restrict__ sort_error, LossDesc loss) {
@@ -146,6 +152,7 @@ render_forward_kernel(int W, int H, int grid_x, uint2* __restrict__ ranges, cons
     __shared__ int s_issued;                    // batches handed to the copy engine so far
     __shared__ uint8_t s_list[kWarps][kFwdRecs];
     __shared__ uint32_t s_tv[kWarps][kFwdRecs];
+    __shared__ uint32_t s_av[kWarps][kFwdRecs];     // per listed instance: lanes that blended it (-> warp mask)
 
     const int tile = blockIdx.x;
     const int tile_x = tile % grid_x, tile_y = tile / grid_x;
@@ -158,8 +165,11 @@ render_forward_kernel(int W, int H, int grid_x, uint2* __restrict__ ranges, cons
     const float4 patch = patch_of_warp(tile_x, tile_y);
     uint8_t* my_list = s_list[warp];
     uint32_t* my_tv = s_tv[warp];
+    uint32_t* my_av = s_av[warp];
     const uint32_t saturated_a = smem_u32(&s_saturated), issued_a = smem_u32(&s_issued);
     uint32_t tv_a = smem_u32(my_tv);
+    uint32_t av_a = smem_u32(my_av);
+    asm volatile("mov.u32 %0, %0;" : "+r"(av_a));
     asm volatile("mov.u32 %0, %0;" : "+r"(tv_a));     // opaque: keeps ptxas from re-deriving the address in the hot loop
 
     // The sort leaves (first position, ~(last position + 1)) per tile, both 0xFFFFFFFF for a tile without instances;
@@ -209,6 +219,13 @@ render_forward_kernel(int W, int H, int grid_x, uint2* __restrict__ ranges, cons
             const int cnt = min(kFwdRecs, n - b * kFwdRecs);
             const float4* rec = &s_rec[stage][0];
             const int n_live = bin_batch_for_warp<kFwdRecs>(rec, cnt, patch, my_list, lane);
+            // Warp mask for the backward: bit 24 + warp of a record's id word (ids stay below 2^24 when the mask is
+            // in use) says "some pixel of this warp blended this instance". The backward then lists exactly the
+            // instances that matter to the warp instead of re-testing footprints (a quarter of which pass the box
+            // test without blending anything). Set in the GLOBAL copy of the record; the copy in shared memory that
+            // this kernel reads ids from was loaded before and stays clean.
+            uint32_t* id_words = reinterpret_cast<uint32_t*>(records) + 12 * ((size_t)range.x + (size_t)b * kFwdRecs) + 2;
+            const uint32_t warp_bit = warp_mask ? (1u << (24 + warp)) : 0u;
             // n_touched counts pixels that blend a Gaussian while still > 50 % transparent (forward.cu:368-370). T only
             // falls, so once none of the warp's pixels is above 0.5 the vote, its store and the counting below are dead
             // weight for the rest of the tile (most of a deep tile): that case runs a loop without them.
@@ -242,6 +259,9 @@ render_forward_kernel(int W, int H, int grid_x, uint2* __restrict__ ranges, cons
                     const uint32_t tv = __ballot_sync(0xffffffffu, act && test_T > 0.5f);
                     asm volatile("{\n\t.reg .pred p;\n\tsetp.eq.u32 p, %0, 0;\n\t@p st.shared.u32 [%1], %2;\n\t}"
                                  ::"r"(lane), "r"(tv_a + 4u * (uint32_t)k), "r"(tv) : "memory");
+                    const uint32_t av = __ballot_sync(0xffffffffu, act);
+                    asm volatile("{\n\t.reg .pred p;\n\tsetp.eq.u32 p, %0, 0;\n\t@p st.shared.u32 [%1], %2;\n\t}"
+                                 ::"r"(lane), "r"(av_a + 4u * (uint32_t)k), "r"(av) : "memory");
                     if (__all_sync(0xffffffffu, done)) { ++k; break; }
                 }
                 __syncwarp();
@@ -249,6 +269,7 @@ render_forward_kernel(int W, int H, int grid_x, uint2* __restrict__ ranges, cons
                 for (int i = (int)lane; i < k; i += 32) {
                     const int c = __popc(my_tv[i]);
                     if (c) atomicAdd(&n_touched[__float_as_int(rec[3 * my_list[i]].z)], c);
+                    if (warp_bit && my_av[i]) atomicOr(id_words + 12 * my_list[i], warp_bit);
                 }
             } else {
                 for (; k < n_live; ++k) {
@@ -263,6 +284,8 @@ render_forward_kernel(int W, int H, int grid_x, uint2* __restrict__ ranges, cons
                     if (act && test_T < 0.0001f) { done = true; act = false; }
                     if (__any_sync(0xffffffffu, act)) {
                         const float4 r2 = rec[3 * j + 2];
+                        asm volatile("{\n\t.reg .pred p;\n\tsetp.eq.u32 p, %0, 0;\n\t@p st.shared.u32 [%1], %2;\n\t}"
+                                     ::"r"(lane), "r"(av_a + 4u * (uint32_t)k), "r"(1u) : "memory");
                         // same arithmetic, predicated per lane instead of branched
                         const float c0 = ffma(T, fmul(alpha, r2.x), C0), c1 = ffma(T, fmul(alpha, r2.y), C1);
                         const float c2 = ffma(T, fmul(alpha, r2.z), C2), dp = ffma(T, fmul(alpha, r2.w), Dp);
@@ -272,10 +295,16 @@ render_forward_kernel(int W, int H, int grid_x, uint2* __restrict__ ranges, cons
                         Dp = act ? dp : Dp;
                         T = act ? test_T : T;
                         last_contributor = act ? (uint32_t)(b * kFwdRecs + j + 1) : last_contributor;
-                    } else if (__all_sync(0xffffffffu, done)) {
-                        break;
+                    } else {
+                        asm volatile("{\n\t.reg .pred p;\n\tsetp.eq.u32 p, %0, 0;\n\t@p st.shared.u32 [%1], %2;\n\t}"
+                                     ::"r"(lane), "r"(av_a + 4u * (uint32_t)k), "r"(0u) : "memory");
+                        if (__all_sync(0xffffffffu, done)) { ++k; break; }
                     }
                 }
+                __syncwarp();
+                if (warp_bit)
+                    for (int i = (int)lane; i < k; i += 32)
+                        if (my_av[i]) atomicOr(id_words + 12 * my_list[i], warp_bit);
             }
             if (__all_sync(0xffffffffu, done)) {
                 warp_done = true;
@@ -327,18 +356,18 @@ render_forward_kernel(int W, int H, int grid_x, uint2* __restrict__ ranges, cons
     }
 }
 
-void launch_render_forward(int W, int H, int grid_x, int grid_y, uint2* ranges, const float* records,
+void launch_render_forward(int W, int H, int grid_x, int grid_y, uint2* ranges, float* records, int warp_mask,
                            const float* bg, float* final_T, uint32_t* n_contrib, float* out_color, float* out_depth,
                            float* out_opacity, int* n_touched, const uint32_t* sort_error, const LossDesc* loss,
                            cudaStream_t s) {
     if (loss != nullptr)
         render_forward_kernel<true><<<grid_x * grid_y, SPLAT_TILE_PIXELS, 0, s>>>(
-            W, H, grid_x, ranges, records, bg, final_T, n_contrib, out_color, out_depth, out_opacity, n_touched,
-            sort_error, *loss);
+            W, H, grid_x, ranges, records, warp_mask, bg, final_T, n_contrib, out_color, out_depth, out_opacity,
+            n_touched, sort_error, *loss);
     else
         render_forward_kernel<false><<<grid_x * grid_y, SPLAT_TILE_PIXELS, 0, s>>>(
-            W, H, grid_x, ranges, records, bg, final_T, n_contrib, out_color, out_depth, out_opacity, n_touched,
-            sort_error, LossDesc());
+            W, H, grid_x, ranges, records, warp_mask, bg, final_T, n_contrib, out_color, out_depth, out_opacity,
+            n_touched, sort_error, LossDesc());
 }
 
 // =====================================================================================================
@@ -449,7 +478,26 @@ __device__ __forceinline__ void flush_chunk(const float2* __restrict__ uw, const
     }
 }
 
-template <int C>
+// Listing of one staged batch for a warp from the forward's warp mask (bit 24 + warp of the id word): exactly the
+// instances some pixel of the warp blended, in order. Same interface as bin_batch_for_warp.
+template <int kRecords>
+__device__ __forceinline__ int list_batch_by_mask(const float4* rec, int cnt, uint32_t warp, uint8_t* list, uint32_t lane) {
+    int n = 0;
+    const uint32_t lt = (1u << lane) - 1u;
+#pragma unroll
+    for (int r = 0; r < kRecords / 32; ++r) {
+        const int j = r * 32 + (int)lane;
+        bool live = false;
+        if (j < cnt) live = (__float_as_uint(reinterpret_cast<const float*>(rec + 3 * j)[2]) >> (24 + warp)) & 1u;
+        const uint32_t m = __ballot_sync(0xffffffffu, live);
+        if (live) list[n + __popc(m & lt)] = (uint8_t)j;
+        n += __popc(m);
+    }
+    __syncwarp();
+    return n;
+}
+
+template <int C, bool kMask>
 __global__ void __launch_bounds__(SPLAT_TILE_PIXELS, C == 8 ? 5 : 4)
 render_backward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ranges,
                        const float* __restrict__ records, const float* __restrict__ bg,
@@ -528,7 +576,8 @@ render_backward_kernel(int W, int H, int grid_x, const uint2* __restrict__ range
         const float4* rec = &s_rec[stage][0];
         if (lo < warp_last) {
             // only list positions below the warp's deepest contributor matter; bin them against the warp's patch
-            const int n_live = bin_batch_for_warp<kRecs>(rec, min(cnt, warp_last - lo), patch, s_list, lane);
+            const int n_live = kMask ? list_batch_by_mask<kRecs>(rec, min(cnt, warp_last - lo), warp, s_list, lane)
+                                     : bin_batch_for_warp<kRecs>(rec, min(cnt, warp_last - lo), patch, s_list, lane);
             const int lc_rel = last_contributor - lo;      // the pixel's last contributor, relative to this batch
             for (int k = n_live - 1; k >= 0; --k) {
                 const int j = s_list[k];
@@ -540,7 +589,9 @@ render_backward_kernel(int W, int H, int grid_x, const uint2* __restrict__ range
                 const float G0 = expf(power);
                 const float alpha0 = fminf(0.99f, fmul(r1.w, G0));
                 const bool skip = (j >= lc_rel) || (power > 0.0f) || (alpha0 < 1.0f / 255.0f);
-                if (__all_sync(0xffffffffu, skip)) continue;
+                if (!kMask) {        // with the mask every listed instance was blended by some lane
+                    if (__all_sync(0xffffffffu, skip)) continue;
+                }
                 const float4 r2 = rec[3 * j + 2];          // r, g, b, depth
                 // lanes that skip contribute through G = 0 and alpha = 0
                 const float G = skip ? 0.0f : G0;
@@ -558,8 +609,8 @@ render_backward_kernel(int W, int H, int grid_x, const uint2* __restrict__ range
                     "st.shared.v2.f32 [%0], {%1, %2};\n\t"
                     "setp.eq.u32 p, %3, 0;\n\t"
                     "@p st.shared.v4.f32 [%4], {%5, %6, %7, %8};\n\t}"
-                    ::"r"(uw_a), "f"(G * dL_dalpha), "f"(w), "r"(lane), "r"(info_a), "f"(r0.x), "f"(r0.y), "f"(r0.z),
-                      "f"(r0.w)
+                    ::"r"(uw_a), "f"(G * dL_dalpha), "f"(w), "r"(lane), "r"(info_a), "f"(r0.x), "f"(r0.y),
+                      "f"(kMask ? __uint_as_float(__float_as_uint(r0.z) & 0x00FFFFFFu) : r0.z), "f"(r0.w)
                     : "memory");
                 uw_a += L::kRowF2 * 8u;
                 info_a += 16u;
@@ -591,7 +642,7 @@ render_backward_kernel(int W, int H, int grid_x, const uint2* __restrict__ range
     }
 }
 
-template <int C>
+template <int C, bool kMask>
 static void launch_bwd_chunked(int W, int H, int grid_x, int grid_y, const uint2* ranges, const float* records,
                                const float* bg, const float* final_T, const uint32_t* n_contrib, const float* dL_dpix,
                                const float* dL_dpix_depth, float* grad_accum, cudaStream_t s) {
@@ -600,11 +651,11 @@ static void launch_bwd_chunked(int W, int H, int grid_x, int grid_y, const uint2
     int dev = 0;
     cudaGetDevice(&dev);
     if (dev >= 0 && dev < 64 && !configured[dev]) {
-        cudaFuncSetAttribute(render_backward_kernel<C>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        cudaFuncSetAttribute(render_backward_kernel<C, kMask>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                              (int)BwdLayout<C>::kBytes);
         configured[dev] = true;
     }
-    render_backward_kernel<C><<<grid_x * grid_y, SPLAT_TILE_PIXELS, BwdLayout<C>::kBytes, s>>>(
+    render_backward_kernel<C, kMask><<<grid_x * grid_y, SPLAT_TILE_PIXELS, BwdLayout<C>::kBytes, s>>>(
         W, H, grid_x, ranges, records, bg, final_T, n_contrib, dL_dpix, dL_dpix_depth, grad_accum);
 }
 
@@ -622,12 +673,13 @@ static int bwd_variant() {
 }
 
 void launch_render_backward(int W, int H, int grid_x, int grid_y, const uint2* ranges, const float* records,
-                            const float* bg, const float* final_T, const uint32_t* n_contrib, const float* dL_dpix,
-                            const float* dL_dpix_depth, float* grad_accum, cudaStream_t s) {
-    if (bwd_variant() == 8)
-        launch_bwd_chunked<8>(W, H, grid_x, grid_y, ranges, records, bg, final_T, n_contrib, dL_dpix, dL_dpix_depth, grad_accum, s);
-    else
-        launch_bwd_chunked<16>(W, H, grid_x, grid_y, ranges, records, bg, final_T, n_contrib, dL_dpix, dL_dpix_depth, grad_accum, s);
+                            int warp_mask, const float* bg, const float* final_T, const uint32_t* n_contrib,
+                            const float* dL_dpix, const float* dL_dpix_depth, float* grad_accum, cudaStream_t s) {
+#define SPLAT_BWD(C, M) launch_bwd_chunked<C, M>(W, H, grid_x, grid_y, ranges, records, bg, final_T, n_contrib, dL_dpix, \
+                                                 dL_dpix_depth, grad_accum, s)
+    if (bwd_variant() == 8) { if (warp_mask) SPLAT_BWD(8, true); else SPLAT_BWD(8, false); }
+    else { if (warp_mask) SPLAT_BWD(16, true); else SPLAT_BWD(16, false); }
+#undef SPLAT_BWD
 }
 
 }  // namespace splat
