@@ -432,12 +432,12 @@ __device__ __forceinline__ void flush_chunk(const float2* __restrict__ uw, const
     for (int rr = 0; rr < kRows; ++rr) {
         const int row = part * kRows + rr;
         const float2* urow = uw + g * BwdLayout<C>::kRowF2 + row * 8;
-        const float4* drow = dlp + row * 8;
+        const float4* drow = dlp + row;        // dL/dpixel is stored column-major (x * 4 + row), see the kernel
         float S0 = 0.f, Sx = 0.f, Sxx = 0.f;
 #pragma unroll
         for (int x = 0; x < 8; ++x) {
             const float2 v = urow[x];
-            const float4 d = drow[x];
+            const float4 d = drow[4 * x];
             S0 += v.x;
             Sx = fmaf(v.x, (float)x, Sx);
             Sxx = fmaf(v.x, (float)(x * x), Sxx);
@@ -559,7 +559,10 @@ render_backward_kernel(int W, int H, int grid_x, const uint2* __restrict__ range
         dLp0 = dL_dpixels[pix_id]; dLp1 = dL_dpixels[HW + pix_id]; dLp2 = dL_dpixels[2 * HW + pix_id];
         dLpd = dL_dpixels_depth[pix_id];
     }
-    s_dlp[lane] = make_float4(dLp0, dLp1, dLp2, dLpd);     // read back by the other lanes of this warp only
+    // read back by the other lanes of this warp only, in the transposed phase. Column-major (x * 4 + row): the lanes
+    // that work on different patch rows in the same iteration then read neighbouring 16-byte words instead of words
+    // 128 bytes apart in the same banks (4 -> 2 wavefronts per load)
+    s_dlp[(lane & 7) * 4 + (lane >> 3)] = make_float4(dLp0, dLp1, dLp2, dLpd);
     // behind the last Gaussian there is only the background
     float D = T_final * (bg[0] * dLp0 + bg[1] * dLp1 + bg[2] * dLp2);
     // nothing in this warp ever blended anything -> the warp only keeps the ring going
