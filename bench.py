@@ -58,8 +58,8 @@ WORKLOADS = {
 }
 # dram__bytes_read.sum + dram__bytes_write.sum per launch of the render kernels on the default scene, from the
 # ncu --set full capture of this round (the file named here); not re-measured by this run
-TRAFFIC = {"source": "profiles/r02_render_ncu_summary.md (ncu --set full, bench scene, one launch)",
-           "render_backward": 249.2e6, "render_forward": 174.6e6}
+TRAFFIC = {"source": "profiles/r02_render_final_ncu_full.csv (ncu --set full, bench scene, one launch)",
+           "render_backward": 249.2e6, "render_forward": 212.0e6}
 
 
 def parse():
