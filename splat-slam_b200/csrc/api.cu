@@ -224,8 +224,8 @@ int splat_raster_forward_preprocess(int P, int D, int M, int W, int H, const flo
         }
     }
     prof_begin(ST_SCAN, s);
-    launch_depth_sort_and_offsets(P, g, s);   // 2 histogram kernels + 4 sort passes + block sums + scan
-    SPLAT_STAGE_END(ST_SCAN, s, 8);
+    launch_depth_sort_and_offsets(P, g, s);   // histogram kernel + 4 sort passes + block sums (with scan)
+    SPLAT_STAGE_END(ST_SCAN, s, 6);
     lane_end(caller, s);
     SPLAT_CUDA_CHECK_LAUNCH();
     return SPLAT_OK;
@@ -309,7 +309,7 @@ int forward_render_impl(int P, int R, int W, int H, const float* background, con
         }
         prof_begin(ST_SORT, s);
         launch_sort_pairs(b.tkey, b.point_list, b.tkey_alt, b.vals_alt, R, passes, b.sort_scratch, s, &sink);
-        SPLAT_STAGE_END(ST_SORT, s, passes + 2);
+        SPLAT_STAGE_END(ST_SORT, s, passes + 1);
         SPLAT_CUDA_CHECK_LAUNCH();
     }
     (void)colors_precomp;   // colours were folded into the per-Gaussian record by the preprocess kernel

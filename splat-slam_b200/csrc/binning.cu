@@ -9,71 +9,63 @@
 namespace splat {
 
 // ---- offsets -----------------------------------------------------------------------------------------
-// Instance count of every block of 256 Gaussians taken in depth-sorted order.
+// Instance count of every block of 256 Gaussians taken in depth-sorted order; the block that finishes last turns the
+// counts into their exclusive scan (the per-Gaussian offsets themselves never reach HBM: duplicate_with_keys_kernel
+// rebuilds them inside the block). `state`: word 0 receives the total, word 2 is the ticket (zero on entry).
 __global__ void __launch_bounds__(kPreBlock)
-sorted_block_sums_kernel(int P, const uint32_t* __restrict__ order, const uint32_t* __restrict__ tiles_touched,
-                         uint32_t* __restrict__ block_sums) {
+sorted_block_sums_kernel(int P, int nblk, const uint32_t* __restrict__ order, const uint32_t* __restrict__ tiles_touched,
+                         uint32_t* __restrict__ sums, uint32_t* __restrict__ state) {
     __shared__ uint32_t s_warp[kPreBlock / 32];
+    __shared__ bool s_last;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int i = blockIdx.x * kPreBlock + threadIdx.x;
     uint32_t v = (i < P) ? tiles_touched[order[i]] : 0u;
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-    if ((threadIdx.x & 31) == 0) s_warp[threadIdx.x >> 5] = v;
+    if (lane == 0) s_warp[warp] = v;
     __syncthreads();
     if (threadIdx.x == 0) {
         uint32_t s = 0;
 #pragma unroll
         for (int w = 0; w < kPreBlock / 32; ++w) s += s_warp[w];
-        block_sums[blockIdx.x] = s;
+        sums[blockIdx.x] = s;
+        __threadfence();
+        s_last = (atomicAdd(&state[2], 1u) == gridDim.x - 1);
     }
-}
-
-// Exclusive scan of the per-block instance counts; the per-Gaussian offsets themselves never reach HBM
-// (duplicate_with_keys_kernel rebuilds them inside the block).
-__global__ void __launch_bounds__(1024) scan_block_sums_kernel(int nblk, uint32_t* __restrict__ sums,
-                                                               uint32_t* __restrict__ total_out) {
-    __shared__ uint32_t s_warp[32];
-    __shared__ uint32_t s_carry;
-    if (threadIdx.x == 0) s_carry = 0;
     __syncthreads();
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    for (int base = 0; base < nblk; base += 1024) {
-        const int i = base + threadIdx.x;
-        const uint32_t v = (i < nblk) ? sums[i] : 0u;
-        uint32_t inc = v;
+    if (!s_last) return;
+    __threadfence();
+    // exclusive scan of sums[0..nblk): every thread takes a contiguous chunk
+    const int per = (nblk + kPreBlock - 1) / kPreBlock;
+    const int lo = min(nblk, (int)threadIdx.x * per), hi = min(nblk, lo + per);
+    uint32_t chunk = 0;
+    for (int k = lo; k < hi; ++k) chunk += __ldcg(sums + k);
+    uint32_t inc = chunk;
 #pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            const uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
-            if (lane >= o) inc += t;
-        }
-        if (lane == 31) s_warp[warp] = inc;
-        __syncthreads();
-        if (warp == 0) {
-            uint32_t w = s_warp[lane];
-#pragma unroll
-            for (int o = 1; o < 32; o <<= 1) {
-                const uint32_t t = __shfl_up_sync(0xffffffffu, w, o);
-                if (lane >= o) w += t;
-            }
-            s_warp[lane] = w;  // inclusive over warps
-        }
-        __syncthreads();
-        const uint32_t carry = s_carry;
-        const uint32_t warp_off = warp ? s_warp[warp - 1] : 0u;
-        if (i < nblk) sums[i] = carry + warp_off + inc - v;
-        __syncthreads();
-        if (threadIdx.x == 1023) s_carry = carry + s_warp[31];
-        __syncthreads();
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += t;
     }
-    if (threadIdx.x == 0) { sums[nblk] = s_carry; total_out[0] = s_carry; }
+    __syncthreads();
+    if (lane == 31) s_warp[warp] = inc;
+    __syncthreads();
+    uint32_t woff = 0, total = 0;
+#pragma unroll
+    for (int w = 0; w < kPreBlock / 32; ++w) { woff += (w < warp) ? s_warp[w] : 0u; total += s_warp[w]; }
+    uint32_t running = woff + inc - chunk;
+    for (int k = lo; k < hi; ++k) {
+        const uint32_t c = __ldcg(sums + k);
+        sums[k] = running;
+        running += c;
+    }
+    if (threadIdx.x == 0) { sums[nblk] = total; state[0] = total; state[2] = 0u; }
 }
 
 // Depth sort of the Gaussians (4 digit passes over P items, see radix_sort.cu) and the instance offsets in that order.
 void launch_depth_sort_and_offsets(int P, const GeomState& g, cudaStream_t s) {
     launch_sort_pairs(g.dkey, g.order, g.dkey_alt, g.order_alt, P, 4, g.sort_scratch, s);   // even: result in place
     const int nblk = (P + kPreBlock - 1) / kPreBlock;
-    sorted_block_sums_kernel<<<nblk, kPreBlock, 0, s>>>(P, g.order, g.tiles_touched, g.block_sums);
-    scan_block_sums_kernel<<<1, 1024, 0, s>>>(nblk, g.block_sums, g.num_rendered);
+    sorted_block_sums_kernel<<<nblk, kPreBlock, 0, s>>>(P, nblk, g.order, g.tiles_touched, g.block_sums, g.num_rendered);
 }
 
 // ---- key generation ----------------------------------------------------------------------------------

@@ -230,7 +230,7 @@ int launch_knn_mean_dist2(int P, const float* points, void* scratch, float* mean
     launch_sort_pairs(k.key0, k.val0, k.key1, k.val1, P, 4, k.sort_scratch, s);     // 30-bit codes, result in (key0,val0)
     knn_gather_boxes_kernel<<<nbox, kKnnBox, 0, s>>>(P, points, k.val0, k.sorted, k.sub_box, k.box);
     knn_search_kernel<<<nbox * (kKnnBox / 256), 256, 0, s>>>(P, nbox, k.sorted, k.sub_box, k.box, mean_dist2);
-    return 4 + 6;      // + histogram, scan and four one-sweep passes inside launch_sort_pairs
+    return 4 + 5;      // + histogram and four one-sweep passes inside launch_sort_pairs
 }
 
 }  // namespace splat

@@ -14,8 +14,8 @@
 // Each pass is ONE kernel ("one sweep"): it reads its 4096-pair tile once, ranks it with warp-synchronous match_any
 // (no atomics; keys stay in registers), gets the tile's global digit offsets by decoupled look-back over the
 // preceding tiles' published counts (windows of 16 independent loads), reorders the pairs through shared memory and
-// writes each digit run with coalesced stores. The global digit bases of all passes come from one up-front
-// histogram kernel. Tiles take their index from an atomic ticket, so a tile only waits for tiles that are already
+// writes each digit run with coalesced stores. The digit totals of all passes come from one up-front histogram
+// kernel; every tile scans the 256 totals of its pass itself. Tiles take their index from an atomic ticket, so a tile only waits for tiles that are already
 // resident and the look-back cannot deadlock; a bounded spin turns a would-be hang into an error flag.
 #include "common.cuh"
 #include "kernels.h"
@@ -66,26 +66,6 @@ radix_global_hist_kernel(const uint32_t* __restrict__ keys, int n, int passes, u
         const uint32_t c = s_h[p][threadIdx.x];
         if (c) atomicAdd(&ghist[p * kRadix + threadIdx.x], c);
     }
-}
-
-// block p: exclusive scan of pass p's 256 digit totals (in place)
-__global__ void __launch_bounds__(kRadix) radix_global_scan_kernel(uint32_t* __restrict__ ghist) {
-    __shared__ uint32_t s_warp[kRadix / 32];
-    uint32_t* h = ghist + blockIdx.x * kRadix;
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const uint32_t v = h[threadIdx.x];
-    uint32_t inc = v;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-        const uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
-        if (lane >= o) inc += t;
-    }
-    if (lane == 31) s_warp[warp] = inc;
-    __syncthreads();
-    uint32_t woff = 0;
-#pragma unroll
-    for (int w = 0; w < kRadix / 32; ++w) woff += (w < warp) ? s_warp[w] : 0u;
-    h[threadIdx.x] = woff + inc - v;
 }
 
 // ---- one pass ---------------------------------------------------------------------------------------------
@@ -202,7 +182,22 @@ radix_onesweep_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __re
 #pragma unroll
     for (int w = 0; w < kWarps; ++w) woff += (w < warp) ? s_scan[w] : 0u;
     const uint32_t local_base = woff + inc - c;
-    s_goff[d] = gbase[d] + prefix - local_base;
+    // global base of digit d = exclusive scan of the pass's digit totals (raw histogram in, scanned here by every
+    // tile: 256 values, cheaper than a launch of its own)
+    const uint32_t gtot = gbase[d];
+    uint32_t ginc = gtot;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t t = __shfl_up_sync(0xffffffffu, ginc, o);
+        if (lane >= o) ginc += t;
+    }
+    __syncthreads();                      // s_scan is reused
+    if (lane == 31) s_scan[warp] = ginc;
+    __syncthreads();
+    uint32_t gwoff = 0;
+#pragma unroll
+    for (int w = 0; w < kWarps; ++w) gwoff += (w < warp) ? s_scan[w] : 0u;
+    s_goff[d] = (gwoff + ginc - gtot) + prefix - local_base;
 #pragma unroll
     for (int w = 0; w < kWarps; ++w) s_cnt[w][d] += local_base;
     __syncthreads();
@@ -281,7 +276,6 @@ void launch_sort_pairs(uint32_t* k0, uint32_t* v0, uint32_t* k1, uint32_t* v1, i
     uint32_t* states = scratch + 4 * kRadix + 64;
     const int hist_blocks = ntiles < 592 ? ntiles : 592;   // 148 SMs x 4
     radix_global_hist_kernel<<<hist_blocks, kSortThreads, 0, s>>>(k0, n, passes, ghist);
-    radix_global_scan_kernel<<<passes, kRadix, 0, s>>>(ghist);
     uint32_t *kin = k0, *vin = v0, *kout = k1, *vout = v1;
     for (int p = 0; p < passes; ++p) {
         if (sink != nullptr && p == passes - 1)

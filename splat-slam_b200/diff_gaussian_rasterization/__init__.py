@@ -291,6 +291,9 @@ class _RasterizeGaussians(torch.autograd.Function):
         ctx.save_for_backward(colors_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh, geomBuffer,
                               binningBuffer, imgBuffer)
         ctx.mark_non_differentiable(radii, n_touched)
+        # outputs nobody differentiates through (opacity, radii, n_touched; often one of color / depth) arrive as None in
+        # backward instead of as freshly filled zero tensors: three fill kernels and their allocations less per view
+        ctx.set_materialize_grads(False)
         return color, radii, depth, opacity, n_touched
 
     @staticmethod
