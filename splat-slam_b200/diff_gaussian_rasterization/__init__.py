@@ -258,6 +258,19 @@ def _backward_impl(S, means3D, radii, colors_precomp, scales, rotations, cov3Ds_
     return dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations, grad_tau
 
 
+def _pose_grads(grad_tau, shapes):
+    """(grad_rho, grad_theta) from tau = [rho, theta]. The reference hands back (1, 3) tensors and lets autograd sum them
+    down to the parameters' shape (DGR __init__.py:152-171); a 3-element parameter gets its own shape directly, which is
+    the same value without the two reduction kernels."""
+    theta_shape, rho_shape = shapes
+    g_rho, g_theta = grad_tau[:3], grad_tau[3:]
+    g_rho = g_rho.view(rho_shape) if len(rho_shape) and rho_shape.count(1) == len(rho_shape) - 1 and 3 in rho_shape \
+        else g_rho.view(1, -1)
+    g_theta = g_theta.view(theta_shape) if len(theta_shape) and theta_shape.count(1) == len(theta_shape) - 1 \
+        and 3 in theta_shape else g_theta.view(1, -1)
+    return g_rho, g_theta
+
+
 class _RasterizeGaussians(torch.autograd.Function):
     @staticmethod
     def forward(ctx, means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp, theta, rho,
@@ -288,6 +301,7 @@ class _RasterizeGaussians(torch.autograd.Function):
 
         ctx.raster_settings = raster_settings
         ctx.num_rendered = num_rendered
+        ctx.pose_shapes = (tuple(theta.shape), tuple(rho.shape))
         ctx.save_for_backward(colors_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh, geomBuffer,
                               binningBuffer, imgBuffer)
         ctx.mark_non_differentiable(radii, n_touched)
@@ -326,8 +340,7 @@ class _RasterizeGaussians(torch.autograd.Function):
             res = _backward_impl(*args)
         (grad_means2D, grad_colors_precomp, grad_opacities, grad_means3D, grad_cov3Ds_precomp, grad_sh, grad_scales,
          grad_rotations, grad_tau) = res
-        grad_rho = grad_tau[:3].view(1, -1)
-        grad_theta = grad_tau[3:].view(1, -1)
+        grad_rho, grad_theta = _pose_grads(grad_tau, ctx.pose_shapes)
         if not ng[2]:
             grad_sh = None          # computed only for its pose term
         grads = (grad_means3D, grad_means2D, grad_sh, grad_colors_precomp, grad_opacities, grad_scales, grad_rotations,
@@ -357,6 +370,7 @@ class _RasterizeGaussiansLoss(torch.autograd.Function):
         num_rendered, color, radii, geomBuffer, binningBuffer, imgBuffer, depth, opacity, n_touched, sums, dimg, ddepth = res
         ctx.raster_settings = raster_settings
         ctx.num_rendered = num_rendered
+        ctx.pose_shapes = (tuple(theta.shape), tuple(rho.shape))
         ctx.initialization = req.initialization
         ctx.exposure_shapes = (None if exposure_a is None else exposure_a.shape,
                                None if exposure_b is None else exposure_b.shape)
@@ -392,8 +406,7 @@ class _RasterizeGaussiansLoss(torch.autograd.Function):
          grad_rotations, grad_tau) = _backward_impl(S, means3D, radii, colors_precomp, scales, rotations, cov3Ds_precomp,
                                                     up_c, up_d, sh, geomBuffer, ctx.num_rendered, binningBuffer,
                                                     imgBuffer, needs)
-        grad_rho = grad_tau[:3].view(1, -1)
-        grad_theta = grad_tau[3:].view(1, -1)
+        grad_rho, grad_theta = _pose_grads(grad_tau, ctx.pose_shapes)
         if not ng[2]:
             grad_sh = None
         return (grad_means3D, grad_means2D, grad_sh, grad_colors_precomp, grad_opacities, grad_scales, grad_rotations,
