@@ -287,7 +287,9 @@ int splat_raster_priority_lanes(int enable);
  * Mirrors what the parity harness carves out of the reference's buffers (rasterizer_impl.cu:155-194).
  * `keys` and `point_list` (the reference's sorted 64-bit keys and point list) are not needed by the render kernels,
  * which read per-instance records; a forward only materialises them while splat_raster_keep_sort_output is on
- * (enable: 1 on, 0 off, < 0 query; returns the previous setting; library-wide, off by default). */
+ * (enable: 1 on, 0 off, < 0 query; returns the previous setting; library-wide, off by default). The 8 bytes per
+ * instance for the keys are part of splat_raster_binning_bytes only while it is on: query the size and run the forward
+ * under the same setting. */
 int splat_raster_keep_sort_output(int enable);
 typedef struct splat_raster_views {
     const float* depths;              /* [P] */

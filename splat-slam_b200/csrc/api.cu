@@ -171,7 +171,7 @@ size_t splat_raster_image_bytes(int W, int H) {
 size_t splat_raster_binning_bytes(int R) {
     if (R < 0) return 0;
     size_t b = 0;
-    BinningState::carve(nullptr, (size_t)R, &b);
+    BinningState::carve(nullptr, (size_t)R, &b, g_keep_sort_output != 0);
     return b;
 }
 
@@ -289,7 +289,7 @@ int forward_render_impl(int P, int R, int W, int H, const float* background, con
     cudaStream_t s = lane_begin(caller);     // key emission, tile sort and record gather on the side lane, if enabled
     const int gx = grid_dim(W), gy = grid_dim(H);
     GeomState g = GeomState::carve(geom, (size_t)P, nullptr);
-    BinningState b = BinningState::carve(binning, (size_t)R, nullptr);
+    BinningState b = BinningState::carve(binning, (size_t)R, nullptr, g_keep_sort_output != 0);
     ImageState im = ImageState::carve(image, (size_t)W * H, (size_t)gx * gy, nullptr);
     const int passes = tile_sort_passes(gx, gy);
     if (R <= 0) launch_reset_ranges(gx * gy, im.ranges, s);     // otherwise preset by the key-emission kernel
@@ -372,7 +372,7 @@ int splat_raster_backward(int P, int D, int M, int R, int W, int H, const float*
     cudaStream_t s = (cudaStream_t)stream;
     const int gx = grid_dim(W), gy = grid_dim(H);
     GeomState g = GeomState::carve(geom, (size_t)P, nullptr);
-    BinningState b = BinningState::carve(binning, (size_t)R, nullptr);
+    BinningState b = BinningState::carve(binning, (size_t)R, nullptr, g_keep_sort_output != 0);
     ImageState im = ImageState::carve(image, (size_t)W * H, (size_t)gx * gy, nullptr);
     prof_begin(ST_ZERO, s);
     cudaError_t e = cudaMemsetAsync(grad_scratch, 0, sizeof(float) * SPLAT_GRAD_FLOATS * (size_t)P, s);
@@ -592,7 +592,7 @@ int splat_raster_debug_views(int P, int R, int W, int H, void* geom, void* binni
     if (!out || P < 0 || R < 0 || W <= 0 || H <= 0) return SPLAT_ERR_ARG;
     const int gx = grid_dim(W), gy = grid_dim(H);
     GeomState g = GeomState::carve(geom, (size_t)P, nullptr);
-    BinningState b = BinningState::carve(binning, (size_t)R, nullptr);
+    BinningState b = BinningState::carve(binning, (size_t)R, nullptr, true);   // keys: only there if the forward ran with keep_sort_output
     ImageState im = ImageState::carve(image, (size_t)W * H, (size_t)gx * gy, nullptr);
     out->depths = g.depths;
     out->means2D = reinterpret_cast<const float*>(g.means2D);
@@ -664,7 +664,7 @@ int splat_raster_backward_noalloc(int P, int D, int M, int R, int W, int H, cons
     cudaStream_t s = (cudaStream_t)stream;
     const int gx = grid_dim(W), gy = grid_dim(H);
     GeomState g = GeomState::carve(geom, (size_t)P, nullptr);
-    BinningState b = BinningState::carve(binning, (size_t)R, nullptr);
+    BinningState b = BinningState::carve(binning, (size_t)R, nullptr, g_keep_sort_output != 0);
     ImageState im = ImageState::carve(image, (size_t)W * H, (size_t)gx * gy, nullptr);
     // the array still holds the previous call's sums: the part this call accumulates into starts from zero
     e = cudaMemsetAsync(scratch, 0, sizeof(float) * SPLAT_GRAD_FLOATS * (size_t)P, s);

@@ -97,24 +97,25 @@ struct ImageState {
 };
 
 struct BinningState {
-    uint64_t* keys;          // [R] sorted (tile << 32 | depth bits), materialised after the sort for inspection
-    uint32_t* point_list;    // [R] sorted Gaussian ids
-    uint32_t* tkey;          // [R] tile id per instance -> sorted
+    float* records;          // [R * SPLAT_REC_FLOATS] per-instance render records in sorted order: all the backward reads
+    uint32_t* point_list;    // [R] Gaussian id per instance (sort values)
+    uint32_t* tkey;          // [R] tile id per instance (sort keys)
     uint32_t* tkey_alt;      // [R] ping-pong buffers of the tile sort
     uint32_t* vals_alt;      // [R]
-    float* records;          // [R * SPLAT_REC_FLOATS] per-instance render records in sorted order
     uint32_t* sort_scratch;  // [sort_scratch_words(R)]
-    static BinningState carve(void* buf, size_t R, size_t* bytes) {
+    uint64_t* keys;          // [R] the reference's sorted (tile << 32 | depth bits), only carved (LAST, so that nothing
+                             //     else moves) when the caller asked for the sort output to be kept for inspection
+    static BinningState carve(void* buf, size_t R, size_t* bytes, bool with_keys) {
         Carver c(buf);
         BinningState b;
         const size_t Rp = R ? R : 1;
-        b.keys = c.take<uint64_t>(Rp);
+        b.records = c.take<float>(Rp * 12);
         b.point_list = c.take<uint32_t>(Rp);
         b.tkey = c.take<uint32_t>(Rp);
         b.tkey_alt = c.take<uint32_t>(Rp);
         b.vals_alt = c.take<uint32_t>(Rp);
-        b.records = c.take<float>(Rp * 12);
         b.sort_scratch = c.take<uint32_t>(sort_scratch_words(Rp));
+        b.keys = with_keys ? c.take<uint64_t>(Rp) : nullptr;
         if (bytes) *bytes = c.bytes();
         return b;
     }

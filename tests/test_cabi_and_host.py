@@ -50,7 +50,7 @@ def test_size_queries_are_monotone_and_aligned():
     assert L.splat_raster_geom_bytes(-1) == 0
     assert L.splat_raster_image_bytes(1200, 680) >= 1200 * 680 * 8 + 75 * 43 * 8
     assert L.splat_raster_binning_bytes(0) > 0
-    assert L.splat_raster_binning_bytes(4_000_000) >= 4_000_000 * (8 + 4 + 8 + 4 + 48)
+    assert L.splat_raster_binning_bytes(4_000_000) >= 4_000_000 * (48 + 4 * 4)     # records + the two sort pairs
 
 
 def test_argument_errors_without_touching_the_gpu():
