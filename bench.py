@@ -83,7 +83,7 @@ def parse():
     ap.add_argument("--exchange", default="auto", choices=["auto", "nccl", "peer"],
                     help="gradient exchange at N > 1: this library's peer-memory all-reduce kernel or NCCL")
     ap.add_argument("--priority-lanes", type=int, default=1, help="1: short kernels on a high-priority side stream")
-    ap.add_argument("--streams", type=int, default=5,
+    ap.add_argument("--streams", type=int, default=10,
                     help="views of a step are issued round-robin on this many CUDA streams (ours only; the reference "
                          "extension launches on the legacy default stream and always runs with 1)")
     a = ap.parse_args()

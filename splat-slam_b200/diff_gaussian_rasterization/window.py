@@ -134,9 +134,10 @@ class ViewStreams:
     view's latency-bound sort passes and its num_rendered hand-off (the one host sync of a forward) hide under another
     view's render kernels. `fork()` makes the side streams wait for the work queued so far, `join()` makes the
     caller's stream wait for all of them. With n <= 1 everything stays on the caller's stream.
-    Measured on one B200 (bench workload): 1 stream 676 it/s, 3 streams 767, 5 streams with priority lanes 823."""
+    Measured on one B200 (bench workload, round 2): 1 stream 800 it/s, 5 streams with priority lanes 960, one stream per
+    view of the 10-view window 976."""
 
-    def __init__(self, device, n: int = 5, priority_lanes: bool = True):
+    def __init__(self, device, n: int = 10, priority_lanes: bool = True):
         self.device = torch.device(device)
         self.streams = [torch.cuda.Stream(device=self.device) for _ in range(n)] if n > 1 else []
         self._restore = []          # process-wide switches this object flipped, undone by close()

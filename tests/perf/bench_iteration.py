@@ -3,7 +3,7 @@
   reference : the compiled reference rasterizer (oracle/_ref/ref_dgr) driven the way the reference drives it —
               activations inside every render call, torch mapping loss per view, isotropic loss, ONE backward over the
               summed loss, the boolean-index densification loop, torch.optim.Adam for the Gaussians and the keyframes;
-  ours      : fused activations once per iteration, this library's rasterizer with the views on five streams, the
+  ours      : fused activations once per iteration, this library's rasterizer with one stream per view, the
               mapping loss evaluated inside each render (LOSS=kernel: stand-alone fused kernel), per-view backward, fused densification stats / visibility, GaussianAdam for both optimizers.
 
     gpurun -- 'python tests/perf/bench_iteration.py'          # prints ms per iteration for each arm
@@ -106,7 +106,7 @@ def iteration_reference(st, mod, do_step=True):
     return vis
 
 
-streams = ViewStreams(dev, int(os.environ.get("STREAMS", 5)))
+streams = ViewStreams(dev, int(os.environ.get("STREAMS", 10)))
 LOSS_IN_RENDER = os.environ.get("LOSS", "attached") == "attached"     # LOSS=kernel: the stand-alone fused loss kernel
 CFG = {"Training": {"alpha": 0.95, "rgb_boundary_threshold": 0.01, "ssim_loss": False}}
 
