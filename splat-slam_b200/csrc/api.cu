@@ -5,6 +5,7 @@
 
 #include <atomic>
 #include <cmath>
+#include <cstdlib>
 #include <map>
 #include <mutex>
 #include <utility>
@@ -88,6 +89,12 @@ const char* kStageNames[ST_COUNT] = {"preprocess_forward", "depth_sort_and_offse
                                      "tile_sort_records_ranges", "render_forward", "zero_grad_scratch",
                                      "render_backward", "preprocess_backward"};
 int g_keep_sort_output = 0;
+// The forward-to-backward warp mask lives in bits 24..31 of the records' id words: clouds of 2^24 Gaussians or more
+// run without it (footprint test in the backward). SPLAT_NO_WARP_MASK=1 forces that path for any size (tests).
+int use_warp_mask(int P) {
+    static const int off = [] { const char* e = getenv("SPLAT_NO_WARP_MASK"); return (e && atoi(e) != 0) ? 1 : 0; }();
+    return (!off && P < kWarpMaskMaxGaussians) ? 1 : 0;
+}
 std::atomic<unsigned long long> g_launches{0};
 int g_prof = 0;
 bool profiling_enabled() { return g_prof != 0; }
@@ -317,7 +324,7 @@ int forward_render_impl(int P, int R, int W, int H, const float* background, con
     s = caller;
     SPLAT_CUDA_CHECK_LAUNCH();
     prof_begin(ST_RENDER_FWD, s);
-    launch_render_forward(W, H, gx, gy, im.ranges, b.records, P < kWarpMaskMaxGaussians ? 1 : 0, background, im.final_T, im.n_contrib, out_color,
+    launch_render_forward(W, H, gx, gy, im.ranges, b.records, use_warp_mask(P), background, im.final_T, im.n_contrib, out_color,
                           out_depth, out_opacity, n_touched, R > 0 ? sort_error_flag(b.sort_scratch) : nullptr, loss, s);
     SPLAT_STAGE_END(ST_RENDER_FWD, s, 1);
     SPLAT_CUDA_CHECK_LAUNCH();
@@ -380,7 +387,7 @@ int splat_raster_backward(int P, int D, int M, int R, int W, int H, const float*
     if (e != cudaSuccess) return (int)e;
     if (R > 0) {
         prof_begin(ST_RENDER_BWD, s);
-        launch_render_backward(W, H, gx, gy, im.ranges, b.records, P < kWarpMaskMaxGaussians ? 1 : 0, background, im.final_T, im.n_contrib, dL_dout_color,
+        launch_render_backward(W, H, gx, gy, im.ranges, b.records, use_warp_mask(P), background, im.final_T, im.n_contrib, dL_dout_color,
                                dL_dout_depth, grad_scratch, s);
         SPLAT_STAGE_END(ST_RENDER_BWD, s, 1);
         SPLAT_CUDA_CHECK_LAUNCH();
@@ -670,7 +677,7 @@ int splat_raster_backward_noalloc(int P, int D, int M, int R, int W, int H, cons
     e = cudaMemsetAsync(scratch, 0, sizeof(float) * SPLAT_GRAD_FLOATS * (size_t)P, s);
     if (e != cudaSuccess) return (int)e;
     if (R > 0) {
-        launch_render_backward(W, H, gx, gy, im.ranges, b.records, P < kWarpMaskMaxGaussians ? 1 : 0, background, im.final_T, im.n_contrib, dL_dout_color,
+        launch_render_backward(W, H, gx, gy, im.ranges, b.records, use_warp_mask(P), background, im.final_T, im.n_contrib, dL_dout_color,
                                dL_dout_depth, scratch, s);
         g_launches += 1;
         SPLAT_CUDA_CHECK_LAUNCH();

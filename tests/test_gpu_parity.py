@@ -329,6 +329,20 @@ def test_debug_mode_checks_every_stage_and_names_the_failing_one(tmp_path, monke
     assert torch.equal(again["color"], plain["color"])
 
 
+def test_without_the_warp_mask_in_a_fresh_process():
+    """Clouds of 2^24 Gaussians or more cannot carry the forward-to-backward warp mask in their id words and use the
+    footprint test in the backward instead. SPLAT_NO_WARP_MASK=1 forces that path; it is read once per process, so the
+    cases run in a child process."""
+    import subprocess
+    import sys
+    env = dict(os.environ, SPLAT_NO_WARP_MASK="1")
+    r = subprocess.run([sys.executable, "-m", "pytest", os.path.abspath(__file__), "-x", "-q", "-m", "gpu", "-k",
+                        "outputs_and_gradients_vs_reference_extension or vs_golden_vectors or stress_footprint"],
+                       capture_output=True, text=True, env=env, timeout=900)
+    assert r.returncode == 0, r.stdout[-3000:]
+    assert " passed" in r.stdout
+
+
 def test_non_default_stream_and_repeatability():
     m = T.load_ours()
     case = T.make_case(camera="small", P=4000, view_k=2)
