@@ -12,6 +12,7 @@ One process per GPU, `torch.distributed` (NCCL over NVLink on the GPU box, gloo 
 from __future__ import annotations
 
 import contextlib
+import os
 from typing import Callable, Dict, List, Optional, Sequence
 
 import torch
@@ -83,6 +84,8 @@ class FlatGrads:
             hdl = symm_mem.rendezvous(store, group=(group if group is not None else dist.group.WORLD))
             ptrs = [int(x) for x in hdl.buffer_ptrs]
             mc = int(getattr(hdl, "multicast_ptr", 0) or 0)
+            if os.environ.get("SPLAT_NO_MULTIMEM"):      # tests: the plain peer load / store kernel on a multicast-capable box
+                mc = 0
             if len(ptrs) != world:
                 raise RuntimeError("rendezvous returned %d buffers for %d ranks" % (len(ptrs), world))
             self._peer = dict(hdl=hdl, ptrs=ptrs, mc=mc, world=world, rank=dist.get_rank(group), count=padded)

@@ -335,12 +335,18 @@ def test_without_the_warp_mask_in_a_fresh_process():
     cases run in a child process."""
     import subprocess
     import sys
-    env = dict(os.environ, SPLAT_NO_WARP_MASK="1")
+    env = dict(os.environ, SPLAT_NO_WARP_MASK="1", SPLAT_BWD_CHUNK="16")      # also the other chunk size of the backward
     r = subprocess.run([sys.executable, "-m", "pytest", os.path.abspath(__file__), "-x", "-q", "-m", "gpu", "-k",
                         "outputs_and_gradients_vs_reference_extension or vs_golden_vectors or stress_footprint"],
                        capture_output=True, text=True, env=env, timeout=900)
     assert r.returncode == 0, r.stdout[-3000:]
     assert " passed" in r.stdout
+    # chunk 16 WITH the mask
+    env = dict(os.environ, SPLAT_BWD_CHUNK="16")
+    r = subprocess.run([sys.executable, "-m", "pytest", os.path.abspath(__file__), "-x", "-q", "-m", "gpu", "-k",
+                        "outputs_and_gradients_vs_reference_extension or vs_golden_vectors"],
+                       capture_output=True, text=True, env=env, timeout=900)
+    assert r.returncode == 0, r.stdout[-3000:]
 
 
 def test_non_default_stream_and_repeatability():
