@@ -326,7 +326,8 @@ unsigned long long splat_raster_debug_sync_count(int reset);
 unsigned long long splat_raster_launch_count(int reset);
 
 /* Per-stage timing with CUDA events recorded on the launching stream. Off by default; when on, each stage is
- * bracketed by two event records and harvested lazily. Returns the previous setting. */
+ * bracketed by two event records and harvested lazily. Returns the previous setting. A measurement aid for ONE host
+ * thread driving ONE device: the event slots are process-wide and not synchronised (the launch counter is atomic). */
 int splat_raster_profile(int enable);
 int splat_raster_stage_count(void);
 const char* splat_raster_stage_name(int stage);
