@@ -174,6 +174,9 @@ class Workload:
         if scaling == "weak":
             self.view_ids = [args.view_offset + rank * args.views + i for i in range(args.views)]
             self.global_views = args.views * world
+        elif scaling == "weak_same_poses":      # every rank renders the SAME poses: per-GPU work exactly fixed
+            self.view_ids = [args.view_offset + i for i in range(args.views)]
+            self.global_views = args.views * world
         else:
             self.view_ids = partition_views(args.views, world, rank)
             self.global_views = args.views
@@ -545,6 +548,15 @@ def main():
                             "ceiling_speedup_vs_1gpu": args.views / per_rank,
                             "note": "BASELINE config 4: one 10-keyframe window, views round-robin over the ranks"}
         ws.streams.close()
+    # ---- weak scaling with exactly equal work per rank (every rank renders rank 0's poses): separates the cost of the
+    # exchange and of sharing the node from the load imbalance between different pose sets
+    if kind == "ours" and not args.no_extras and ref_world > 1 and args.scaling == "weak":
+        wu = Workload(mod, args, device, wrank, ref_world, "weak_same_poses", shared=wl, streams=args.streams)
+        ms_u = timed(wu.step_resident, args.steps, args.warmup, device, ref_world) / args.steps
+        extras["weak_same_poses"] = {"value": wu.global_views / (ms_u * 1e-3), "unit": "it/s", "ms_per_step": ms_u,
+                                     "note": "every rank renders the poses of rank 0 (equal work per GPU); compare with "
+                                             "the 1-GPU value for the efficiency net of load imbalance"}
+        wu.streams.close()
     if args.verify and kind == "ours":
         wl.set_streams(args.streams, bool(args.priority_lanes))
         extras["verify"] = verify_exchange(wl, args, device, wrank, ref_world)
