@@ -268,8 +268,8 @@ render_forward_kernel(int W, int H, int grid_x, uint2* __restrict__ ranges, floa
                 // one atomic per (warp, Gaussian) with votes instead of one per pixel
                 for (int i = (int)lane; i < k; i += 32) {
                     const int c = __popc(my_tv[i]);
-                    if (c) atomicAdd(&n_touched[__float_as_int(rec[3 * my_list[i]].z)], c);
-                    if (warp_bit && my_av[i]) atomicOr(id_words + 12 * my_list[i], warp_bit);
+                    if (c) asm volatile("red.global.add.s32 [%0], %1;" ::"l"(n_touched + __float_as_int(rec[3 * my_list[i]].z)), "r"(c) : "memory");
+                    if (warp_bit && my_av[i]) asm volatile("red.global.or.b32 [%0], %1;" ::"l"(id_words + 12 * my_list[i]), "r"(warp_bit) : "memory");
                 }
             } else {
                 for (; k < n_live; ++k) {
@@ -304,7 +304,7 @@ render_forward_kernel(int W, int H, int grid_x, uint2* __restrict__ ranges, floa
                 __syncwarp();
                 if (warp_bit)
                     for (int i = (int)lane; i < k; i += 32)
-                        if (my_av[i]) atomicOr(id_words + 12 * my_list[i], warp_bit);
+                        if (my_av[i]) asm volatile("red.global.or.b32 [%0], %1;" ::"l"(id_words + 12 * my_list[i]), "r"(warp_bit) : "memory");
             }
             if (__all_sync(0xffffffffu, done)) {
                 warp_done = true;
